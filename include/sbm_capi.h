@@ -1,0 +1,148 @@
+/* sbm_capi.h -- C ABI of the B200 (sm_100a) implementation of line2Dup::Detector::match.
+ *
+ * This is the drop-in boundary: plain C, pointers and sizes only.  The C++ drop-in header
+ * (include/line2Dup.h) and the Python mirror (shape_based_matching_b200/detector.py) sit on top of
+ * exactly these entry points; nothing below this line runs on the CPU except list ordering.
+ *
+ * Every function returns 0 on success or a negative sbm_status; sbm_last_error() gives the text
+ * (thread-local).  There is no CPU fallback: without a CUDA device sbm_create fails with
+ * SBM_ERR_CUDA.
+ *
+ * Reference interface each entry point replaces (file:line in /root/reference):
+ *   sbm_create              Detector::Detector(int, std::vector<int>, float, float)   line2Dup.cpp:1056-1076
+ *   sbm_set_class_templates Detector::readClass / addTemplate (template storage)      line2Dup.cpp:1299-1353,1507-1546
+ *   sbm_match               Detector::match                                           line2Dup.cpp:1078-1150
+ *   sbm_match_candidates    Detector::match without its sort/unique tail              line2Dup.cpp:1124-1140
+ *   sbm_match_device        same pipeline, frame already resident in HBM              (bench `value`, multi-GPU)
+ *   sbm_get_intermediate    the locals of match(): quantized / spread / response maps / linear memories
+ *                                                                                    line2Dup.cpp:1106-1117
+ *   sbm_similarity_map      similarity / similarity_64                                line2Dup.cpp:807-858,924-984
+ *   sbm_similarity_local    similarityLocal / similarityLocal_64                      line2Dup.cpp:860-922,986-1048
+ */
+#ifndef SBM_CAPI_H
+#define SBM_CAPI_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct sbm_ctx sbm_ctx;
+
+typedef enum sbm_status {
+    SBM_OK = 0,
+    SBM_ERR_BAD_ARG = -1,   /* cv::Error::StsBadArg / CV_Assert in the reference */
+    SBM_ERR_CUDA = -2,      /* CUDA runtime failure, or no device */
+    SBM_ERR_CAPACITY = -3,  /* caller's output buffer too small; *n_out holds the needed size */
+    SBM_ERR_STATE = -4      /* e.g. intermediate requested before any frame was processed */
+} sbm_status;
+
+/* One Template of a TemplatePyramid (line2Dup.h:131-153), without its feature vector. */
+typedef struct sbm_template_desc {
+    int32_t width, height, tl_x, tl_y;
+    int32_t num_features; /* features.size(); the features follow each other in the sbm_feature array */
+} sbm_template_desc;
+
+/* line2Dup::Feature (line2Dup.h:116-129) without theta (theta is not used by match()). */
+typedef struct sbm_feature {
+    int32_t x, y, label;
+} sbm_feature;
+
+/* line2Dup::Match (line2Dup.h:222-255); class_idx indexes the caller's class list. */
+typedef struct sbm_match_rec {
+    int32_t x, y;
+    float similarity;
+    int32_t class_idx;
+    int32_t template_id;
+} sbm_match_rec;
+
+typedef enum sbm_intermediate {
+    SBM_QUANTIZED = 0, /* u8  [h_l][w_l]                      ColorGradientPyramid::quantize  :446-450 */
+    SBM_SPREAD = 1,    /* u8  [h_l][w_l]                      spread                          :616-630 */
+    SBM_RESPONSE = 2,  /* u8  [8][h_l][w_l]                   computeResponseMaps             :637-747 */
+    SBM_LINEAR = 3,    /* u8  [8][T*T][(w_l/T)*(h_l/T)]       linearize                       :749-777 */
+    SBM_PYRAMID_SRC = 4 /* u8 [h_l][w_l][channels]            cv::pyrDown chain               :424-444 */
+} sbm_intermediate;
+
+const char *sbm_last_error(void);
+/* Compile-time facts, so that a loader can verify it got the sm_100a build. */
+const char *sbm_build_info(void);
+
+/* T[levels]: spread/stride per pyramid level (default {4,8}); weak/strong: magnitude thresholds
+ * (defaults 30/60); num_features: the training-time feature budget (kept for API parity; match() does
+ * not use it).  device: CUDA ordinal. */
+int sbm_create(const int *T, int levels, float weak, float strong, int num_features, int device, sbm_ctx **out);
+int sbm_destroy(sbm_ctx *ctx);
+
+/* Replace the template set of class slot `class_idx` (0..). desc has n_templates*levels entries ordered
+ * [template][level]; feats holds sum(num_features) entries in the same order.  n_templates == 0 removes
+ * the class.  Templates with >= 8192 features at any level are rejected (line2Dup.cpp:811,1195). */
+int sbm_set_class_templates(sbm_ctx *ctx, int class_idx, int n_templates, const sbm_template_desc *desc,
+                            const sbm_feature *feats);
+int sbm_clear_templates(sbm_ctx *ctx);
+int sbm_num_templates(sbm_ctx *ctx, int class_idx);
+
+/* Detector::match.  img: 8-bit, channels 1 or 3 (interleaved), `stride` bytes per row (0 = packed);
+ * w,h must satisfy the reference's asserts at every level (h_l % T_l == 0, w_l % T_l == 0,
+ * h_l*w_l % 16 == 0).  mask: NULL or u8 [h][w] (packed).  class_idx[n_classes]: class slots to match in
+ * this order (NULL / 0 = all slots in ascending order, i.e. the caller's std::map order).
+ * out[cap] receives the final list: sorted by (similarity desc, template_id asc) and de-duplicated by the
+ * same std::sort/std::unique calls as the reference, fed in the reference's serial candidate order. */
+int sbm_match(sbm_ctx *ctx, const uint8_t *img, int w, int h, int channels, size_t stride, const uint8_t *mask,
+              float threshold, const int *class_idx, int n_classes, sbm_match_rec *out, int cap, int *n_out);
+
+/* Same, but stops before sort/unique: the candidate list in the order the reference appends it with one
+ * OpenMP thread (class order, template_id ascending, coarse scan order). */
+int sbm_match_candidates(sbm_ctx *ctx, const uint8_t *img, int w, int h, int channels, size_t stride,
+                         const uint8_t *mask, float threshold, const int *class_idx, int n_classes,
+                         sbm_match_rec *out, int cap, int *n_out);
+
+/* Device-resident variant: d_img is a packed u8 [h][w][channels] frame in HBM.  The whole pipeline is
+ * enqueued on `stream` (a cudaStream_t, or NULL for the context's own stream) and nothing is copied to
+ * the host.  Results stay on the device:
+ *   d_records: sbm_device_rec[cap]   (unordered; see sbm_device_rec)
+ *   d_count  : uint32[2]             ([0] = number of records produced (may exceed cap), [1] = overflow flag)
+ * Either may be NULL, in which case the context's internal buffers are used (sbm_device_results). */
+typedef struct sbm_device_rec {
+    int32_t x, y;          /* level-0 top-left of the match */
+    float similarity;
+    uint32_t template_gid; /* global template index: templates of class slot 0 first, then slot 1, ... */
+    uint32_t order_key;    /* coarse scan index j: orders candidates of one template like the reference */
+} sbm_device_rec;
+
+int sbm_match_device(sbm_ctx *ctx, const void *d_img, int w, int h, int channels, const void *d_mask, float threshold,
+                     const int *class_idx, int n_classes, void *d_records, int cap, void *d_count, void *stream);
+int sbm_device_results(sbm_ctx *ctx, void **d_records, void **d_count, int *cap);
+/* Turn device records (copied to the host by the caller, e.g. after an NCCL allgather) into the final
+ * list: same ordering + std::sort + std::unique as sbm_match.  finalize != 0 applies sort/unique. */
+int sbm_finalize_records(sbm_ctx *ctx, const sbm_device_rec *recs, int n, const int *class_idx, int n_classes,
+                         int finalize, sbm_match_rec *out, int cap, int *n_out);
+
+/* Copy an intermediate of the most recent frame to host memory `dst` (`bytes` must match exactly;
+ * pass dst == NULL to query the size through *bytes_needed).  SPREAD and RESPONSE are only materialised
+ * when sbm_set_debug(ctx, 1) was called before the frame. */
+int sbm_set_debug(sbm_ctx *ctx, int enable);
+int sbm_get_intermediate(sbm_ctx *ctx, int level, int kind, void *dst, size_t bytes, size_t *bytes_needed);
+
+/* Raw u16 [H][W] similarity sums of one template at the coarsest level on the most recent frame. */
+int sbm_similarity_map(sbm_ctx *ctx, int class_idx, int template_id, uint16_t *dst, size_t bytes);
+/* Raw u16 [16][16] local sums at pyramid level `level` around centre (x,y) (level coordinates). */
+int sbm_similarity_local(sbm_ctx *ctx, int class_idx, int template_id, int level, int x, int y, uint16_t *dst);
+
+/* Counters of the most recent frame: [0] coarse evaluations (sum over matched templates of
+ * in-image features * template_positions), [1] coarse candidates, [2] local evaluations,
+ * [3] records after refinement, [4] kernels launched by the most recent call. */
+int sbm_last_stats(sbm_ctx *ctx, uint64_t stats[8]);
+
+/* Device time of the most recent match call in milliseconds (CUDA events on the launching stream;
+ * needs sbm_set_timing(ctx, 1)): [0] whole pipeline, [1] front end (orientations .. linear memories),
+ * [2] similarity + refinement. */
+int sbm_last_timing(sbm_ctx *ctx, float ms[4]);
+int sbm_set_timing(sbm_ctx *ctx, int enable);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SBM_CAPI_H */

@@ -1,0 +1,73 @@
+"""In-tree build of the native pieces (no JIT cache: the .so files travel with the repo snapshot).
+
+    python -m shape_based_matching_b200.build          # CUDA library + host C++ check + oracle
+"""
+import os
+import subprocess
+import sys
+
+PKG = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(PKG)
+LIB = os.path.join(PKG, "libsbm_b200.so")
+NVCC = os.environ.get("SBM_NVCC", "/usr/local/cuda/bin/nvcc")
+# the environment may export CXX=/opt/gcc/bin/g++ (no libgomp): always use the system compiler
+HOST_CXX = "/usr/bin/g++"
+
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+    "-ccbin", HOST_CXX, "-shared", "-Xcompiler", "-fPIC", "-Xptxas", "-v",
+]
+
+
+def _run(cmd, **kw):
+    print("+", " ".join(cmd), flush=True)
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, **kw)
+    if r.returncode != 0:
+        print(r.stdout)
+        raise RuntimeError("build step failed: " + " ".join(cmd))
+    return r.stdout
+
+
+def _stale(target, sources):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(s) > t for s in sources)
+
+
+def build_cuda(force=False):
+    srcs = [os.path.join(PKG, "csrc", f) for f in ("sbm_capi.cu", "sbm_kernels.cuh")] + [
+        os.path.join(ROOT, "include", "sbm_capi.h")
+    ]
+    if force or _stale(LIB, srcs):
+        out = _run([NVCC] + NVCC_FLAGS + ["-I" + os.path.join(ROOT, "include"), "-I" + os.path.join(PKG, "csrc"),
+                                           srcs[0], "-o", LIB])
+        with open(os.path.join(PKG, "csrc", "ptxas_info.txt"), "w") as f:
+            f.write(out)
+    return LIB
+
+
+def build_oracle(force=False):
+    """Build the CHECKER (test infrastructure): the C restatement and, where the reference tree exists,
+    the reference's own code (oracle/_ref).  Building it is not using it."""
+    odir = os.path.join(ROOT, "oracle")
+    port_src = os.path.join(odir, "sbm_oracle.cpp")
+    port = os.path.join(odir, "libsbm_oracle.so")
+    if os.path.exists(port_src) and (force or _stale(port, [port_src])):
+        _run(["make", "-C", odir, "port"])
+    ref = os.path.join(odir, "_ref", "libsbm_ref.so")
+    if os.path.exists("/root/reference/line2Dup.cpp"):
+        deps = [os.path.join(odir, "ref_driver.cpp"), os.path.join(odir, "shim", "opencv2", "imgproc.hpp"),
+                os.path.join(ROOT, "include", "sbm", "cv_compat.hpp")]
+        if force or _stale(ref, deps):
+            _run(["make", "-C", odir, "ref"])
+
+
+def build_all(force=False):
+    build_cuda(force)
+    build_oracle(force)
+
+
+if __name__ == "__main__":
+    build_all(force="--force" in sys.argv)
+    print("ok:", LIB)
