@@ -1,0 +1,375 @@
+#!/usr/bin/env python
+"""bench.py -- Detector::match hot path on B200: template-pixel evaluations/s and ms/frame.
+
+    python bench.py [--gpus N --steps K --warmup W] [--impl reference] [--frames B]
+
+Workload (BASELINE.json metric, config M1 of BASELINE.md): 1024x1024x3 frames x 360 rotation templates
+(test/case1 templates 0..359, 131/71 features at the two pyramid levels, T={4,8}, threshold 90).  One
+STEP = one pass of the whole hot path (orientations -> spread -> response maps -> linear memories ->
+similarity -> thresholded candidates -> local refinement) over a batch of B distinct synthetic frames
+(default 64 frames = 192 MiB of input per rank, larger than the 126 MB L2, so no frame is cache-warm).
+
+  value   template-pixel evaluations/s, frames already resident in HBM, results left in HBM,
+          timed with CUDA events on the launching stream (max over ranks).
+  e2e     same metric through the public API with HOST buffers: Detector.match_records(frame) per
+          frame from pinned host memory to the final host list (H2D + pipeline + D2H + sort/unique).
+  N > 1   frames are sharded (rank r owns its own B frames, all 360 templates: weak scaling); the per-
+          frame candidate lists are exchanged at the end of the step with ONE NCCL all_gather -- the only
+          exchange the path has.
+  --impl reference   the reference's own CPU code (oracle/_ref = /root/reference/line2Dup.cpp compiled
+          verbatim, OpenMP over all host threads) on a bounded sample of the same frames.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "template_pixel_evals_per_s"
+UNIT = "evals/s"
+THRESHOLD = 90.0
+W = H = 1024
+C = 3
+N_TEMPLATES = 360
+REC_CAP = 4096  # per-frame record capacity of the device-resident path
+
+
+def load_workload():
+    from _fixtures import load_case, load_templates
+
+    case = load_case("m1")
+    cid, tdesc, feats, nf = load_templates("case1[:360]")
+    return case["img"], cid, tdesc, feats, nf
+
+
+def make_frames(base, n, seed0):
+    """n distinct frames derived from the M1 frame: cyclic shifts (multiples of 16 keep every true match
+    on the coarse grid) + a per-frame sprinkle of low-amplitude noise."""
+    out = np.empty((n,) + base.shape, np.uint8)
+    for i in range(n):
+        rng = np.random.default_rng(seed0 + i)
+        dy, dx = int(rng.integers(0, 64)) * 16, int(rng.integers(0, 64)) * 16
+        f = np.roll(base, (dy, dx), axis=(0, 1)).astype(np.int16)
+        f += rng.integers(-2, 3, f.shape, dtype=np.int16)
+        out[i] = np.clip(f, 0, 255).astype(np.uint8)
+    return out
+
+
+def coarse_evals_per_frame(tdesc, feats, T=8, w=512, h=512):
+    """sum over templates of (features inside the coarse image) * template_positions (line2Dup.cpp:813-857)."""
+    Wc, Hc = w // T, h // T
+    total = 0
+    fo = 0
+    for t in range(tdesc.shape[0]):
+        for l in range(tdesc.shape[1]):
+            nf = int(tdesc[t, l, 4])
+            if l == tdesc.shape[1] - 1:
+                f = feats[fo : fo + nf]
+                nv = int(((f[:, 0] >= 0) & (f[:, 0] < w) & (f[:, 1] >= 0) & (f[:, 1] < h)).sum())
+                wf = (int(tdesc[t, l, 0]) - 1) // T + 1
+                hf = (int(tdesc[t, l, 1]) - 1) // T + 1
+                tp = (Hc - hf) * Wc + (Wc - wf) + 1
+                total += nv * max(tp, 0)
+            fo += nf
+    return total
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        super().__init__(daemon=True)
+        self.gpu = gpu_index
+        self.rows = []
+        self.proc = None
+
+    def run(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                self.rows.append([x.strip() for x in line.split(",")])
+        except Exception:
+            pass
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+        self.join(timeout=2)
+        sm = [float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
+        reasons = set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            if len(r) >= 9:
+                for k, nm in enumerate(names):
+                    if r[5 + k].lower().startswith("active"):
+                        reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def reference_arm(args, rank, world):
+    """The reference's own CPU implementation of the path, all host threads (rank 0 only)."""
+    if rank != 0:
+        return
+    from oracle import ref
+
+    base, cid, tdesc, feats, nf = load_workload()
+    cores = os.cpu_count() or 1
+    det = ref.RefDetector(nf, (4, 8))
+    det.add_class(cid, tdesc, feats)
+    sample = max(1, min(args.ref_frames, args.frames))
+    frames = make_frames(base, sample, 1000)
+    # evaluations of the sample: coarse (closed form) + local (256 * nf per coarse candidate), counted by
+    # the reference's own similarity maps (oracle/ref_driver.cpp ref_eval_counts)
+    evals = 0
+    for f in frames:
+        ce, _cc, le = det.eval_counts(f, THRESHOLD, [cid])
+        assert ce == coarse_evals_per_frame(tdesc, feats)
+        evals += ce + le
+    for _ in range(args.warmup):
+        det.match(frames[0], THRESHOLD, [cid], omp_threads=cores)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        for f in frames:
+            det.match(f, THRESHOLD, [cid], omp_threads=cores)
+    dt = (time.perf_counter() - t0) / args.steps
+    value = evals / dt
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt * 1e3, "ms_per_frame": dt * 1e3 / sample, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "M1: 1024x1024x3 frames x 360 templates (case1 ids 0..359, 131/71 features, T={4,8}, thr 90)",
+                   "frames_per_step": sample, "evals_per_frame": evals / sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference",
+                         "sample": "%d frames/step x %d steps, Detector::match verbatim (oracle/_ref, -O3 -mavx2 -mfma -fopenmp, "
+                                   "OpenCV ops through the scalar shim)" % (sample, args.steps)},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--frames", type=int, default=64, help="frames per step per rank")
+    ap.add_argument("--ref-frames", type=int, default=4, help="frames per step of the CPU reference arm")
+    ap.add_argument("--cpu-baseline-frames", type=int, default=8)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        reference_arm(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+
+    from shape_based_matching_b200 import DEVICE_REC, Detector
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    base, cid, tdesc, feats, nf = load_workload()
+    B = args.frames
+    frames = make_frames(base, B, 1000 + rank * B)
+    det = Detector(nf, (4, 8), 30.0, 60.0, device=local_rank)
+    det.setClassTemplates(cid, tdesc, feats)
+
+    # ---- parity guard: the frame the fixture was generated from must still give the golden list ----
+    from _fixtures import load_case
+
+    gold = load_case("m1")
+    got = det.match_records(gold["img"], THRESHOLD, [cid])
+    if len(got) != len(gold["matches"]) or not np.array_equal(got["x"], gold["matches"]["x"]) or not np.array_equal(
+            got["similarity"].view(np.uint32), gold["matches"]["similarity"].view(np.uint32)):
+        raise SystemExit("bench.py: CUDA path disagrees with the golden reference list; refusing to time it")
+
+    stream = torch.cuda.current_stream()
+    sptr = stream.cuda_stream
+    d_frames = torch.from_numpy(frames).to(dev)  # [B, H, W, C] resident in HBM
+    rec_bytes = DEVICE_REC.itemsize
+    d_recs = torch.zeros((B, REC_CAP * rec_bytes), dtype=torch.uint8, device=dev)
+    d_cnt = torch.zeros((B, 2), dtype=torch.int32, device=dev)
+    if world > 1:
+        g_recs = torch.zeros((world * B, REC_CAP * rec_bytes), dtype=torch.uint8, device=dev)
+        g_cnt = torch.zeros((world * B, 2), dtype=torch.int32, device=dev)
+
+    def step_device():
+        for i in range(B):
+            det.match_device(d_frames[i].data_ptr(), W, H, C, THRESHOLD, [cid], d_records=d_recs[i].data_ptr(), cap=REC_CAP,
+                             d_count=d_cnt[i].data_ptr(), stream=sptr)
+        if world > 1:  # the path's one exchange: compact candidate lists, allgathered over NVLink
+            dist.all_gather_into_tensor(g_cnt, d_cnt)
+            dist.all_gather_into_tensor(g_recs, d_recs)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # evaluation count of one step on this rank (coarse: closed form; local: counted by the kernels)
+    local_evals = 0
+    for i in range(B):
+        det.match_records(frames[i], THRESHOLD, [cid])
+        st = det.last_stats()
+        local_evals += st["local_evals"]
+    launches_per_frame = st["gpu_launches"]
+    coarse = st["coarse_evals"]
+    assert coarse == coarse_evals_per_frame(tdesc, feats), "evaluation count mismatch"
+    evals_step_rank = coarse * B + local_evals
+
+    for _ in range(args.warmup):
+        step_device()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record(stream)
+    for _ in range(args.steps):
+        step_device()
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    t = torch.tensor([ms, float(evals_step_rank)], dtype=torch.float64, device=dev)
+    if world > 1:
+        tm = t.clone()
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        ts = t.clone()
+        dist.all_reduce(ts, op=dist.ReduceOp.SUM)
+        ms, evals_step = float(tm[0]), float(ts[1])
+    else:
+        evals_step = float(evals_step_rank)
+    ms_per_step = ms / args.steps
+    value = evals_step / (ms_per_step * 1e-3)
+
+    # ---- per-kernel device times (separate pass with event timing on) for the roofline ----
+    det.set_timing(True)
+    kt = {"front_ms": [], "similarity_ms": [], "refine_ms": [], "total_ms": []}
+    for i in range(B):
+        det.match_device(d_frames[i].data_ptr(), W, H, C, THRESHOLD, [cid], d_records=d_recs[i].data_ptr(), cap=REC_CAP,
+                         d_count=d_cnt[i].data_ptr(), stream=sptr)
+        torch.cuda.synchronize()
+        tm_ = det.last_timing()
+        for k in kt:
+            kt[k].append(tm_[k])
+    det.set_timing(False)
+    kmean = {k: float(np.mean(v)) for k, v in kt.items()}
+
+    # ---- end to end through the public API: pinned host frame -> final host list, every frame ----
+    pinned = torch.from_numpy(frames).pin_memory()
+    pin_np = pinned.numpy()
+    n_final = 0
+    for i in range(min(B, 8)):
+        det.match_records(pin_np[i], THRESHOLD, [cid])
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        for i in range(B):
+            n_final += len(det.match_records(pin_np[i], THRESHOLD, [cid]))
+    torch.cuda.synchronize()
+    e2e_s = (time.perf_counter() - t0) / args.steps
+    te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_s = float(te[0])
+    e2e_value = evals_step / e2e_s
+    d2h = (16 * 4 + 2048 * rec_bytes) * B  # counters + head of the record buffer, per frame
+    clocks = sampler.stop() if rank == 0 else None
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
+    # dominant kernel = k_similarity: 1 algorithmic byte per coarse evaluation
+    sim_gbs = coarse / (kmean["similarity_ms"] * 1e-3) / 1e9
+    front_bytes = (W * H * C + 8 * W * H) + (W * H * C // 4 + 8 * W * H // 4)  # read c + write 8 per pixel, both levels
+    front_gbs = front_bytes / (kmean["front_ms"] * 1e-3) / 1e9
+    roofline = {
+        "kernel": "k_similarity", "bound": "hbm", "achieved": sim_gbs, "peak": hbm_peak, "unit": "GB/s",
+        "frac": sim_gbs / hbm_peak, "traffic": None, "peak_source": peak_src,
+        "algorithmic_bytes_per_launch": coarse, "avg_launch_ms": kmean["similarity_ms"],
+        "note": "linear memories of the coarse level (2 MiB) are L2-resident: frac > 1 of the HBM copy peak is possible",
+        "other_kernels": {"front_end(5 launches)": {"ms": kmean["front_ms"], "algorithmic_bytes": front_bytes, "GB/s": front_gbs,
+                                                    "frac_of_hbm_peak": front_gbs / hbm_peak},
+                          "k_refine": {"ms": kmean["refine_ms"]}, "pipeline_total_ms": kmean["total_ms"]},
+    }
+
+    cpu_baseline = None
+    if not args.no_cpu_baseline:
+        try:
+            from oracle import ref
+
+            cores = os.cpu_count() or 1
+            rd = ref.RefDetector(nf, (4, 8))
+            rd.add_class(cid, tdesc, feats)
+            nsamp = max(1, min(args.cpu_baseline_frames, B))
+            rd.match(frames[0], THRESHOLD, [cid], omp_threads=cores)
+            t0 = time.perf_counter()
+            for i in range(nsamp):
+                rd.match(frames[i], THRESHOLD, [cid], omp_threads=cores)
+            dt = time.perf_counter() - t0
+            split = rd.time(frames[0], THRESHOLD, [cid], omp_threads=cores, iters=2)
+            cpu_baseline = {"value": (evals_step_rank / B) * nsamp / dt, "unit": UNIT, "cores": cores, "kind": "reference",
+                            "sample": "%d of the %d frames, Detector::match verbatim via oracle/_ref (-O3 -mavx2 -mfma "
+                                      "-fopenmp; OpenCV ops through the scalar shim)" % (nsamp, B),
+                            "ms_per_frame": dt / nsamp * 1e3, "ms_front": split["ms_front"], "ms_match": split["ms_match"]}
+        except Exception as ex:  # the checker is optional on a box without oracle/_ref
+            cpu_baseline = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": "unavailable: %s" % ex}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_per_step, "ms_per_frame": ms_per_step / B, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "M1: 1024x1024x3 frames x 360 templates (case1 ids 0..359, 131/71 features, T={4,8}, thr 90)",
+                   "frames_per_step_per_gpu": B, "sharding": "frames (each rank its own frames, all templates)",
+                   "l2_policy": "inputs larger than L2: %d MiB of distinct frames per step per GPU" % (B * W * H * C >> 20),
+                   "evals_per_frame": evals_step / (B * world), "final_matches_per_step": n_final // max(1, args.steps)},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": B * W * H * C, "d2h_bytes_per_step": d2h,
+                "ms_per_frame": e2e_s / B * 1e3},
+        "gpu_launches": launches_per_frame * B * args.steps,
+        "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline,
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -138,7 +138,7 @@ int sbm_last_stats(sbm_ctx *ctx, uint64_t stats[8]);
 
 /* Device time of the most recent match call in milliseconds (CUDA events on the launching stream;
  * needs sbm_set_timing(ctx, 1)): [0] whole pipeline, [1] front end (orientations .. linear memories),
- * [2] similarity + refinement. */
+ * [2] coarse similarity kernel (+threshold/compaction), [3] local refinement. */
 int sbm_last_timing(sbm_ctx *ctx, float ms[4]);
 int sbm_set_timing(sbm_ctx *ctx, int enable);
 

@@ -183,3 +183,11 @@ class RefDetector:
             )
         )
         return dict(ms_front=f.value, ms_match=m.value, ms_total=t.value, n_matches=n.value)
+
+    def eval_counts(self, img, threshold, class_ids=()):
+        """-> (coarse evaluations, coarse candidates, local evaluations) of one frame (ref_driver.cpp ref_eval_counts)."""
+        img, a = _img_args(img)
+        ce, cc, le = C.c_ulonglong(), C.c_ulonglong(), C.c_ulonglong()
+        self._chk(self.L.ref_eval_counts(self.h, *a, C.c_float(threshold), ",".join(class_ids).encode(),
+                                         C.byref(ce), C.byref(cc), C.byref(le)))
+        return ce.value, cc.value, le.value

@@ -458,4 +458,58 @@ int ref_cv_erode3(const uint8_t *img, int w, int hh, uint8_t *out)
     return 0;
     REF_CATCH
 }
+
+// Workload counters of one frame, derived from the reference's own functions:
+//   coarse = sum_t (features inside the coarse image) * template_positions      (line2Dup.cpp:813-857)
+//   coarse_cands = positions with score > threshold                              (line2Dup.cpp:1200-1216)
+//   local  = 256 * sum over coarse candidates of features at level L-2           (line2Dup.cpp:1254-1261)
+// (deeper pyramids: only the first refinement level is counted).
+int ref_eval_counts(void *h, const uint8_t *img, int w, int hh, int c, float thr, const char *class_csv,
+                    unsigned long long *coarse, unsigned long long *coarse_cands, unsigned long long *local)
+{
+    REF_TRY
+    Probe *p = (Probe *)h;
+    Probe::Front f;
+    p->front(wrap(img, w, hh, c), cv::Mat(), f, false);
+    const int L = p->pyramidLevels();
+    const int T = p->Ts().back();
+    const cv::Size sz = f.sizes.back();
+    const int W = sz.width / T, H = sz.height / T;
+    unsigned long long ce = 0, cc = 0, le = 0;
+    for (auto &id : p->resolve(splitIds(class_csv)))
+    {
+        const auto &tps = p->templates().at(id);
+        for (size_t t = 0; t < tps.size(); ++t)
+        {
+            const Template &tc = tps[t].back();
+            int wf = (tc.width - 1) / T + 1, hf = (tc.height - 1) / T + 1;
+            int tp = (H - hf) * W + (W - wf) + 1;
+            int nv = 0;
+            for (auto &ft : tc.features)
+                if (!(ft.x < 0 || ft.x >= sz.width || ft.y < 0 || ft.y >= sz.height))
+                    ++nv;
+            ce += (unsigned long long)nv * (unsigned long long)std::max(tp, 0);
+            cv::Mat sim;
+            if (tc.features.size() < 64)
+            {
+                similarity_64(f.lm.back()[0], tc, sim, sz, T);
+                sim.convertTo(sim, CV_16U);
+            }
+            else
+                similarity(f.lm.back()[0], tc, sim, sz, T);
+            int nf = (int)tc.features.size();
+            unsigned long long n = 0;
+            for (int r = 0; r < sim.rows; ++r)
+                for (int q = 0; q < sim.cols; ++q)
+                    if ((sim.at<ushort>(r, q) * 100.f) / (4 * nf) > thr)
+                        ++n;
+            cc += n;
+            if (L >= 2)
+                le += n * 256ull * (unsigned long long)tps[t][L - 2].features.size();
+        }
+    }
+    *coarse = ce, *coarse_cands = cc, *local = le;
+    return 0;
+    REF_CATCH
+}
 }

@@ -123,7 +123,7 @@ struct sbm_ctx
     uint32_t h_recs_cap = 0;
 
     bool debug = false, timing = false;
-    cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     float last_ms[4] = {0, 0, 0, 0};
     uint64_t stats[8] = {0};
     int launches = 0;
@@ -439,6 +439,8 @@ int enqueueFrame(sbm_ctx *c, const uint8_t *d_img, const uint8_t *d_mask, float 
                                                out_cnt, out_cap, nullptr);
         ++launches;
     }
+    if (c->timing)
+        CK(cudaEventRecord(c->ev[3], st));
     Cand *in = out;
     uint32_t in_cap = out_cap;
     uint32_t *in_cnt = out_cnt;
@@ -610,12 +612,6 @@ int matchHost(sbm_ctx *c, const uint8_t *img, int w, int h, int ch, size_t strid
         }
         if (rc)
             return rc;
-        if (c->timing)
-        {
-            cudaEventElapsedTime(&c->last_ms[0], c->ev[0], c->ev[2]);
-            cudaEventElapsedTime(&c->last_ms[1], c->ev[0], c->ev[1]);
-            cudaEventElapsedTime(&c->last_ms[2], c->ev[1], c->ev[2]);
-        }
         c->stats[0] = c->coarse_evals;
         c->stats[1] = c->h_counts[0];
         memcpy(&c->stats[2], &c->h_counts[10], sizeof(uint64_t));
@@ -660,7 +656,7 @@ int sbm_create(const int *T, int levels, float weak, float strong, int num_featu
     c->weak = weak, c->strong = strong, c->num_features = num_features;
     c->lv.resize(levels);
     CK(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
-    for (int i = 0; i < 3; ++i)
+    for (int i = 0; i < 4; ++i)
         CK(cudaEventCreate(&c->ev[i]));
     *out = c;
     return 0;
@@ -690,7 +686,7 @@ int sbm_destroy(sbm_ctx *c)
         cudaFreeHost(c->h_counts);
     if (c->h_recs)
         cudaFreeHost(c->h_recs);
-    for (int i = 0; i < 3; ++i)
+    for (int i = 0; i < 4; ++i)
         if (c->ev[i])
             cudaEventDestroy(c->ev[i]);
     if (c->own_stream)
@@ -938,7 +934,8 @@ int sbm_last_timing(sbm_ctx *c, float ms[4])
         CK(cudaEventSynchronize(c->ev[2]));
         cudaEventElapsedTime(&c->last_ms[0], c->ev[0], c->ev[2]);
         cudaEventElapsedTime(&c->last_ms[1], c->ev[0], c->ev[1]);
-        cudaEventElapsedTime(&c->last_ms[2], c->ev[1], c->ev[2]);
+        cudaEventElapsedTime(&c->last_ms[2], c->ev[1], c->ev[3]);
+        cudaEventElapsedTime(&c->last_ms[3], c->ev[3], c->ev[2]);
     }
     memcpy(ms, c->last_ms, sizeof(c->last_ms));
     return 0;

@@ -234,4 +234,4 @@ class Detector:
     def last_timing(self):
         t = np.zeros(4, np.float32)
         check(self._L.sbm_last_timing(self._h, t.ctypes.data_as(C.c_void_p)))
-        return dict(total_ms=float(t[0]), front_ms=float(t[1]), match_ms=float(t[2]))
+        return dict(total_ms=float(t[0]), front_ms=float(t[1]), similarity_ms=float(t[2]), refine_ms=float(t[3]))
