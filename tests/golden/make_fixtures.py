@@ -111,8 +111,8 @@ def make_cv_pins():
     px = rng.integers(-1020, 1021, 1 << 18).astype(np.float32)
     py = rng.integers(-1020, 1021, 1 << 18).astype(np.float32)
     ax = np.arange(-1020, 1021, dtype=np.float32)
-    px = np.concatenate([px, ax, np.zeros_like(ax), ax, ax, [0]])
-    py = np.concatenate([py, np.zeros_like(ax), ax, ax, -ax, [0]])
+    px = np.concatenate([px, ax, np.zeros_like(ax), ax, ax, [0]]).astype(np.float32)
+    py = np.concatenate([py, np.zeros_like(ax), ax, ax, -ax, [0]]).astype(np.float32)
     d["phase_x"], d["phase_y"] = px, py
     d["phase_deg"] = cv2.phase(px.reshape(1, -1), py.reshape(1, -1), angleInDegrees=True).ravel()
     # convertTo(CV_8U, 16/360): rint half-to-even on float product
