@@ -293,7 +293,9 @@ int ensureTemplates(sbm_ctx *c)
                         o.nf = d.num_features;
                         int wf = (d.width - 1) / T + 1, hf = (d.height - 1) / T + 1;
                         o.tp = (H - hf) * W + (W - wf) + 1;
-                        int nv = 0;
+                        // in-image features only (line2Dup.cpp:836), bucketed by the word shift of their start
+                        // offset so that k_similarity runs four branch-free loops (integer adds commute)
+                        std::vector<uint32_t> cls[4];
                         for (int i = 0; i < d.num_features; ++i)
                         {
                             const sbm_feature &f = cs.feats[fo + i];
@@ -301,9 +303,16 @@ int ensureTemplates(sbm_ctx *c)
                                 continue;
                             if (f.label < 0 || f.label > 7)
                                 return fail(SBM_ERR_BAD_ARG, "feature label %d out of range", f.label);
-                            off.push_back((uint32_t)f.label * T * T * WH + (uint32_t)((f.y % T) * T + f.x % T) * WH +
-                                          (uint32_t)(f.y / T) * W + (uint32_t)(f.x / T));
-                            ++nv;
+                            uint32_t a = (uint32_t)f.label * T * T * WH + (uint32_t)((f.y % T) * T + f.x % T) * WH +
+                                         (uint32_t)(f.y / T) * W + (uint32_t)(f.x / T);
+                            cls[(a >> 2) & 3].push_back(a);
+                        }
+                        int nv = 0;
+                        for (int k = 0; k < 4; ++k)
+                        {
+                            off.insert(off.end(), cls[k].begin(), cls[k].end());
+                            nv += (int)cls[k].size();
+                            o.cls_end[k] = (uint16_t)nv;
                         }
                         o.n_valid = nv;
                     }
