@@ -197,7 +197,7 @@ int ensureShape(sbm_ctx *c, int w, int h, int ch)
         // tail slack: flat addressing lets the last memory be over-read: a whole memory for
         // the coarse scan past template_positions, 16 rows + 16 for the local patch, +8 for the realigning loads
         size_t WH = (size_t)L.W * L.H;
-        L.lm_alloc = L.lm_bytes + std::max(WH, (size_t)16 * L.W + 16) + 64;
+        L.lm_alloc = L.lm_bytes + std::max(WH, (size_t)16 * L.W + 16) + 128;
         CK(cudaMalloc(&L.d_lm, L.lm_alloc));
         CK(cudaMemset(L.d_lm, 0, L.lm_alloc));
         if (c->debug)
@@ -307,12 +307,16 @@ int ensureTemplates(sbm_ctx *c)
                                          (uint32_t)(f.y / T) * W + (uint32_t)(f.x / T);
                             cls[(a >> 2) & 3].push_back(a);
                         }
-                        int nv = 0;
+                        int nv = 0, stored = 0;
                         for (int k = 0; k < 4; ++k)
                         {
-                            off.insert(off.end(), cls[k].begin(), cls[k].end());
                             nv += (int)cls[k].size();
-                            o.cls_end[k] = (uint16_t)nv;
+                            // pad with reads of the zeroed tail (same word shift): adds 0, keeps batches full
+                            while (cls[k].size() % K5_U)
+                                cls[k].push_back((uint32_t)LB.lm_bytes + 4u * k);
+                            off.insert(off.end(), cls[k].begin(), cls[k].end());
+                            stored += (int)cls[k].size();
+                            o.cls_end[k] = (uint16_t)stored;
                         }
                         o.n_valid = nv;
                     }
