@@ -419,11 +419,18 @@ int enqueueFrame(sbm_ctx *c, const uint8_t *d_img, const uint8_t *d_mask, float 
             src = LB.d_src;
             ++launches;
         }
-        dim3 g1((LB.w + K1_TW - 1) / K1_TW, (LB.h + K1_TH - 1) / K1_TH);
-        if (c->c == 3)
-            k_orient<3><<<g1, K1_THREADS, 0, st>>>(src, LB.w, LB.h, d_mask, l, c->w, weak_sq, LB.d_quant);
+        // 64x32 tiles unless that leaves the GPU under two waves of CTAs; then 64x16
+        const bool tall = ((LB.w + K1_TW - 1) / K1_TW) * ((LB.h + 31) / 32) >= 2 * 148;
+        const int th = tall ? 32 : 16;
+        dim3 g1((LB.w + K1_TW - 1) / K1_TW, (LB.h + th - 1) / th);
+        if (c->c == 3 && tall)
+            k_orient<3, 32><<<g1, K1_THREADS, 0, st>>>(src, LB.w, LB.h, d_mask, l, c->w, weak_sq, LB.d_quant);
+        else if (c->c == 3)
+            k_orient<3, 16><<<g1, K1_THREADS, 0, st>>>(src, LB.w, LB.h, d_mask, l, c->w, weak_sq, LB.d_quant);
+        else if (tall)
+            k_orient<1, 32><<<g1, K1_THREADS, 0, st>>>(src, LB.w, LB.h, d_mask, l, c->w, weak_sq, LB.d_quant);
         else
-            k_orient<1><<<g1, K1_THREADS, 0, st>>>(src, LB.w, LB.h, d_mask, l, c->w, weak_sq, LB.d_quant);
+            k_orient<1, 16><<<g1, K1_THREADS, 0, st>>>(src, LB.w, LB.h, d_mask, l, c->w, weak_sq, LB.d_quant);
         dim3 g2((LB.w + K2_PW - 1) / K2_PW, (LB.h + K2_PH - 1) / K2_PH);
         uint8_t *ds = c->debug ? LB.d_spread : nullptr, *dr = c->debug ? LB.d_resp : nullptr;
         if (LB.T == 4)
