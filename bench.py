@@ -11,8 +11,9 @@ similarity -> thresholded candidates -> local refinement) over a batch of B dist
 
   value   template-pixel evaluations/s, frames already resident in HBM, results left in HBM,
           timed with CUDA events on the launching stream (max over ranks).
-  e2e     same metric through the public API with HOST buffers: Detector.match_records(frame) per
-          frame from pinned host memory to the final host list (H2D + pipeline + D2H + sort/unique).
+  e2e     same metric through the public API with HOST buffers: Detector.match_batch(frames) from pinned
+          host memory to the final host lists (H2D + pipeline + D2H + sort/unique for every frame; several
+          frames in flight).  `latency` reports the one-frame-at-a-time numbers next to it.
   N > 1   frames are sharded (rank r owns its own B frames, all 360 templates: weak scaling); the per-
           frame candidate lists are exchanged at the end of the step with ONE NCCL all_gather -- the only
           exchange the path has.
@@ -221,13 +222,20 @@ def main():
         g_recs = torch.zeros((world * B, REC_CAP * rec_bytes), dtype=torch.uint8, device=dev)
         g_cnt = torch.zeros((world * B, 2), dtype=torch.int32, device=dev)
 
+    frame_bytes = W * H * C
+
     def step_device():
-        for i in range(B):
-            det.match_device(d_frames[i].data_ptr(), W, H, C, THRESHOLD, [cid], d_records=d_recs[i].data_ptr(), cap=REC_CAP,
-                             d_count=d_cnt[i].data_ptr(), stream=sptr)
+        # one call: the 64 resident frames are spread over the detector's internal streams (sbm_match_batch_device)
+        det.match_batch_device(d_frames.data_ptr(), frame_bytes, B, W, H, C, THRESHOLD, [cid], d_recs.data_ptr(), REC_CAP,
+                               d_cnt.data_ptr(), sptr)
         if world > 1:  # the path's one exchange: compact candidate lists, allgathered over NVLink
             dist.all_gather_into_tensor(g_cnt, d_cnt)
             dist.all_gather_into_tensor(g_recs, d_recs)
+
+    def step_device_serial():
+        for i in range(B):
+            det.match_device(d_frames[i].data_ptr(), W, H, C, THRESHOLD, [cid], d_records=d_recs[i].data_ptr(), cap=REC_CAP,
+                             d_count=d_cnt[i].data_ptr(), stream=sptr)
 
     def barrier():
         if world > 1:
@@ -271,10 +279,20 @@ def main():
     ms_per_step = ms / args.steps
     value = evals_step / (ms_per_step * 1e-3)
 
-    # ---- per-kernel device times (separate pass with event timing on) for the roofline ----
+    # ---- single-stream latency per frame (frames strictly one after the other) ----
+    for _ in range(2):
+        step_device_serial()
+    torch.cuda.synchronize()
+    e0.record(stream)
+    step_device_serial()
+    e1.record(stream)
+    torch.cuda.synchronize()
+    serial_ms_per_frame = e0.elapsed_time(e1) / B
+
+    # ---- per-stage device times (event timing on; the events themselves cost a few us per stage) ----
     det.set_timing(True)
     kt = {"front_ms": [], "similarity_ms": [], "refine_ms": [], "total_ms": []}
-    for i in range(B):
+    for i in range(min(B, 16)):
         det.match_device(d_frames[i].data_ptr(), W, H, C, THRESHOLD, [cid], d_records=d_recs[i].data_ptr(), cap=REC_CAP,
                          d_count=d_cnt[i].data_ptr(), stream=sptr)
         torch.cuda.synchronize()
@@ -283,18 +301,19 @@ def main():
             kt[k].append(tm_[k])
     det.set_timing(False)
     kmean = {k: float(np.mean(v)) for k, v in kt.items()}
+    # the roofline kernel alone: back-to-back launches of the pipeline's own k_similarity grid between two events
+    sim_ms = det.time_similarity(THRESHOLD, iters=50)
 
     # ---- end to end through the public API: pinned host frame -> final host list, every frame ----
     pinned = torch.from_numpy(frames).pin_memory()
     pin_np = pinned.numpy()
     n_final = 0
-    for i in range(min(B, 8)):
-        det.match_records(pin_np[i], THRESHOLD, [cid])
+    frame_list = [pin_np[i] for i in range(B)]
+    det.match_batch(frame_list, THRESHOLD, [cid])
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        for i in range(B):
-            n_final += len(det.match_records(pin_np[i], THRESHOLD, [cid]))
+        n_final += sum(len(r) for r in det.match_batch(frame_list, THRESHOLD, [cid]))
     torch.cuda.synchronize()
     e2e_s = (time.perf_counter() - t0) / args.steps
     te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
@@ -302,7 +321,12 @@ def main():
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_s = float(te[0])
     e2e_value = evals_step / e2e_s
-    d2h = (16 * 4 + 2048 * rec_bytes) * B  # counters + head of the record buffer, per frame
+    # latency of ONE blocking Detector.match call (H2D + pipeline + D2H + sort/unique), frames one at a time
+    t0 = time.perf_counter()
+    for i in range(B):
+        det.match_records(pin_np[i], THRESHOLD, [cid])
+    single_call_ms = (time.perf_counter() - t0) / B * 1e3
+    d2h = (16 * 4 + 1024 * rec_bytes) * B  # counters + head of the record buffer, per frame
     clocks = sampler.stop() if rank == 0 else None
 
     if rank != 0:
@@ -318,17 +342,20 @@ def main():
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
     # dominant kernel = k_similarity: 1 algorithmic byte per coarse evaluation
-    sim_gbs = coarse / (kmean["similarity_ms"] * 1e-3) / 1e9
+    sim_gbs = coarse / (sim_ms * 1e-3) / 1e9
     front_bytes = (W * H * C + 8 * W * H) + (W * H * C // 4 + 8 * W * H // 4)  # read c + write 8 per pixel, both levels
     front_gbs = front_bytes / (kmean["front_ms"] * 1e-3) / 1e9
     roofline = {
         "kernel": "k_similarity", "bound": "hbm", "achieved": sim_gbs, "peak": hbm_peak, "unit": "GB/s",
         "frac": sim_gbs / hbm_peak, "traffic": None, "peak_source": peak_src,
-        "algorithmic_bytes_per_launch": coarse, "avg_launch_ms": kmean["similarity_ms"],
+        "algorithmic_bytes_per_launch": coarse, "avg_launch_ms": sim_ms,
+        "how": "50 back-to-back launches of the pipeline's k_similarity grid between two CUDA events on the launching stream (sbm_time_similarity)",
         "note": "linear memories of the coarse level (2 MiB) are L2-resident: frac > 1 of the HBM copy peak is possible",
         "other_kernels": {"front_end(5 launches)": {"ms": kmean["front_ms"], "algorithmic_bytes": front_bytes, "GB/s": front_gbs,
                                                     "frac_of_hbm_peak": front_gbs / hbm_peak},
-                          "k_refine": {"ms": kmean["refine_ms"]}, "pipeline_total_ms": kmean["total_ms"]},
+                          "k_similarity(+events)": {"ms": kmean["similarity_ms"]},
+                          "k_refine": {"ms": kmean["refine_ms"]}, "pipeline_total_ms": kmean["total_ms"],
+                          "note": "stage times bracketed by CUDA events inside one frame; each bracket adds a few us"},
     }
 
     cpu_baseline = None
@@ -362,7 +389,8 @@ def main():
                    "l2_policy": "inputs larger than L2: %d MiB of distinct frames per step per GPU" % (B * W * H * C >> 20),
                    "evals_per_frame": evals_step / (B * world), "final_matches_per_step": n_final // max(1, args.steps)},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": B * W * H * C, "d2h_bytes_per_step": d2h,
-                "ms_per_frame": e2e_s / B * 1e3},
+                "ms_per_frame": e2e_s / B * 1e3, "api": "Detector.match_batch(64 pinned host frames) -> 64 final host lists"},
+        "latency": {"device_ms_per_frame_single_stream": serial_ms_per_frame, "match_call_ms_host_to_host": single_call_ms},
         "gpu_launches": launches_per_frame * B * args.steps,
         "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline,
     }

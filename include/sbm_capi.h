@@ -13,7 +13,9 @@
  *   sbm_set_class_templates Detector::readClass / addTemplate (template storage)      line2Dup.cpp:1299-1353,1507-1546
  *   sbm_match               Detector::match                                           line2Dup.cpp:1078-1150
  *   sbm_match_candidates    Detector::match without its sort/unique tail              line2Dup.cpp:1124-1140
+ *   sbm_match_batch         Detector::match over a stream of frames (config 5)        line2Dup.cpp:1078-1150, test_jabil.cpp:314-374
  *   sbm_match_device        same pipeline, frame already resident in HBM              (bench `value`, multi-GPU)
+ *   sbm_match_batch_device  same, a batch of resident frames kept in flight together
  *   sbm_get_intermediate    the locals of match(): quantized / spread / response maps / linear memories
  *                                                                                    line2Dup.cpp:1106-1117
  *   sbm_similarity_map      similarity / similarity_64                                line2Dup.cpp:807-858,924-984
@@ -99,6 +101,17 @@ int sbm_match_candidates(sbm_ctx *ctx, const uint8_t *img, int w, int h, int cha
                          const uint8_t *mask, float threshold, const int *class_idx, int n_classes,
                          sbm_match_rec *out, int cap, int *n_out);
 
+/* Detector::match over n_frames frames of one shape (the streaming configuration; the reference's caller loops
+ * over the images of a directory, test_jabil.cpp:314-374).  Several frames are kept in flight: the H2D copy
+ * of frame i+1 overlaps the kernels of frame i.  imgs[i]: host pointer of frame i (pinned memory makes the copies
+ * truly asynchronous); masks: NULL, or n_frames pointers (entries may be NULL).  The final lists are
+ * concatenated in out[cap]; frame i owns out[frame_begin[i] .. frame_begin[i+1]) (frame_begin has n_frames+1
+ * entries).  Every list is exactly what sbm_match returns for that frame.  On SBM_ERR_CAPACITY
+ * frame_begin[n_frames] is the capacity needed. */
+int sbm_match_batch(sbm_ctx *ctx, const uint8_t *const *imgs, const uint8_t *const *masks, int n_frames, int w, int h,
+                    int channels, size_t stride, float threshold, const int *class_idx, int n_classes, sbm_match_rec *out,
+                    int cap, int *frame_begin);
+
 /* Device-resident variant: d_img is a packed u8 [h][w][channels] frame in HBM.  The whole pipeline is
  * enqueued on `stream` (a cudaStream_t, or NULL for the context's own stream) and nothing is copied to
  * the host.  Results stay on the device:
@@ -114,6 +127,12 @@ typedef struct sbm_device_rec {
 
 int sbm_match_device(sbm_ctx *ctx, const void *d_img, int w, int h, int channels, const void *d_mask, float threshold,
                      const int *class_idx, int n_classes, void *d_records, int cap, void *d_count, void *stream);
+/* A batch of resident frames: frame i = d_imgs + i*frame_stride bytes.  Frames are spread over the context's
+ * internal streams (forked from / joined to `stream`), so neighbouring frames overlap on the GPU.
+ * d_records: sbm_device_rec[n_frames][cap_per_frame]; d_counts: uint32[n_frames][2] (as in sbm_match_device). */
+int sbm_match_batch_device(sbm_ctx *ctx, const void *d_imgs, size_t frame_stride, int n_frames, int w, int h, int channels,
+                           float threshold, const int *class_idx, int n_classes, void *d_records, int cap_per_frame,
+                           void *d_counts, void *stream);
 int sbm_device_results(sbm_ctx *ctx, void **d_records, void **d_count, int *cap);
 /* Turn device records (copied to the host by the caller, e.g. after an NCCL allgather) into the final
  * list: same ordering + std::sort + std::unique as sbm_match.  finalize != 0 applies sort/unique. */
@@ -141,6 +160,9 @@ int sbm_last_stats(sbm_ctx *ctx, uint64_t stats[8]);
  * [2] coarse similarity kernel (+threshold/compaction), [3] local refinement. */
 int sbm_last_timing(sbm_ctx *ctx, float ms[4]);
 int sbm_set_timing(sbm_ctx *ctx, int enable);
+/* Average device time of ONE k_similarity launch (the roofline kernel) on the most recent frame's linear memories:
+ * `iters` back-to-back launches of the pipeline's own grid between two CUDA events on the launching stream. */
+int sbm_time_similarity(sbm_ctx *ctx, float threshold, int iters, float *ms_per_launch);
 
 #ifdef __cplusplus
 }

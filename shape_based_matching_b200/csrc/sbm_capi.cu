@@ -1,10 +1,15 @@
 // sbm_capi.cu -- host side of the C ABI declared in include/sbm_capi.h.
 //
-// Owns the device context of one Detector: template SoA per pyramid level, per-shape scratch (pyramid
-// sources, quantised images, linear memories, candidate ping-pong buffers) and the stream the seven
-// kernels of a frame are enqueued on.  The only CPU work per frame is ordering the (tiny) candidate list
-// the way the reference's serial loop produces it and running the same std::sort / std::unique
-// (line2Dup.cpp:1143-1145).  There is no CPU implementation of any pipeline stage in this library.
+// One sbm_ctx = one Detector on one GPU.  It owns
+//   * the template set as device SoA (per pyramid level) and, per frame shape, the coarse-level feature
+//     offsets into the linear memories;
+//   * SBM_SLOTS frame slots.  A slot is everything one in-flight frame needs -- a stream, the pyramid sources,
+//     quantised images, linear memories, candidate ping-pong buffers, pinned result staging -- so that
+//     sbm_match_batch can keep several frames in flight: the H2D copy of frame i+1 and the kernels of frame i
+//     overlap, and the small kernels of neighbouring frames share the GPU.  Slot 0 serves the single-frame calls.
+// The only CPU work per frame is ordering the (tiny) candidate list the way the reference's serial loop
+// produces it and running the same std::sort / std::unique (line2Dup.cpp:1143-1145).  There is no CPU
+// implementation of any pipeline stage in this library.
 #include "sbm_capi.h"
 #include "sbm_kernels.cuh"
 
@@ -43,6 +48,10 @@ int fail(int code, const char *fmt, ...)
             return fail(SBM_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
     } while (0)
 
+constexpr int SBM_SLOTS = 4;
+constexpr int COUNT_WORDS = 16; // [0..levels-1] stage counts, [10..11] u64 local evaluations
+constexpr uint32_t HEAD_RECS = 1024;
+
 struct ClassSet
 {
     int n = 0;
@@ -50,17 +59,26 @@ struct ClassSet
     std::vector<sbm_feature> feats;
 };
 
-struct LevelBuf
+// geometry of one pyramid level for the current frame shape
+struct LevelGeom
 {
     int T = 0, w = 0, h = 0, W = 0, H = 0;
+    size_t lm_bytes = 0, lm_alloc = 0;
+};
+
+// templates of one pyramid level on the device
+struct LevelTempl
+{
+    TemplLevel *d_tl = nullptr;
+    Feat *d_feats = nullptr;
+};
+
+struct LevelBuf
+{
     uint8_t *d_src = nullptr; // level >= 1 (level 0 is the frame itself)
     uint8_t *d_quant = nullptr;
     uint8_t *d_lm = nullptr;
-    size_t lm_bytes = 0, lm_alloc = 0;
     uint8_t *d_spread = nullptr, *d_resp = nullptr; // debug taps
-    // templates at this level
-    TemplLevel *d_tl = nullptr;
-    Feat *d_feats = nullptr;
 };
 
 template <typename T> void freeDev(T *&p)
@@ -69,6 +87,33 @@ template <typename T> void freeDev(T *&p)
         cudaFree(p);
     p = nullptr;
 }
+
+struct Slot
+{
+    cudaStream_t stream = nullptr;
+    uint64_t shape_gen = 0; // generation of ctx geometry these buffers were allocated for
+    bool debug_bufs = false;
+    std::vector<LevelBuf> lv;
+    uint8_t *d_frame = nullptr; // staging for host frames
+    size_t frame_alloc = 0;
+    uint8_t *d_mask = nullptr;
+    size_t mask_alloc = 0;
+    const uint8_t *last_src0 = nullptr;
+    // candidates
+    uint32_t cap = 1u << 16;
+    Cand *d_buf[2] = {nullptr, nullptr};
+    uint32_t *d_counts = nullptr;
+    Cand *d_final = nullptr; // where the last stage of the most recent frame wrote
+    uint32_t *d_final_count = nullptr;
+    uint32_t final_cap = 0;
+    // pinned host staging
+    uint32_t *h_counts = nullptr;
+    Cand *h_recs = nullptr;
+    uint32_t h_recs_cap = 0;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    bool have_frame = false;
+    int launches = 0;
+};
 } // namespace
 
 struct sbm_ctx
@@ -78,23 +123,19 @@ struct sbm_ctx
     float weak = 30.f, strong = 60.f;
     int num_features = 63;
     int levels = 0;
-    cudaStream_t own_stream = nullptr;
     std::mutex mu;
 
     std::vector<ClassSet> classes;
     std::vector<uint32_t> gid_begin; // per class slot (+ total)
     bool templates_dirty = true;
     uint32_t n_templates = 0;
+    std::vector<LevelTempl> tl;
 
     // frame shape
     int w = 0, h = 0, c = 0;
-    bool have_frame = false;
-    std::vector<LevelBuf> lv;
-    uint8_t *d_frame = nullptr; // staging for host frames
-    size_t frame_alloc = 0;
-    uint8_t *d_mask = nullptr;
-    size_t mask_alloc = 0;
-    const uint8_t *last_src0 = nullptr;
+    uint64_t shape_gen = 0;
+    std::vector<LevelGeom> geom;
+    Slot slot[SBM_SLOTS];
 
     // coarse level, per (templates, shape)
     bool coarse_dirty = true;
@@ -109,34 +150,16 @@ struct sbm_ctx
     uint32_t n_active = 0;
     uint64_t coarse_evals = 0;
 
-    // candidates
-    uint32_t cap = 1u << 18;
-    Cand *d_buf[2] = {nullptr, nullptr};
-    uint32_t *d_counts = nullptr; // [0..levels-1] stage counts, [8] overflow, [10..11] u64 local evals
-    Cand *d_final = nullptr;      // where the last stage of the most recent frame wrote
-    uint32_t *d_final_count = nullptr;
-    uint32_t final_cap = 0;
-
-    // host staging (pinned)
-    uint32_t *h_counts = nullptr;
-    Cand *h_recs = nullptr;
-    uint32_t h_recs_cap = 0;
-
     bool debug = false, timing = false;
-    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     float last_ms[4] = {0, 0, 0, 0};
     uint64_t stats[8] = {0};
-    int launches = 0;
 };
 
 namespace
 {
-constexpr int COUNT_WORDS = 16;
-constexpr uint32_t HEAD_RECS = 2048;
-
-void freeShape(sbm_ctx *c)
+void freeSlotShape(Slot &s)
 {
-    for (auto &l : c->lv)
+    for (auto &l : s.lv)
     {
         freeDev(l.d_src);
         freeDev(l.d_quant);
@@ -144,6 +167,7 @@ void freeShape(sbm_ctx *c)
         freeDev(l.d_spread);
         freeDev(l.d_resp);
     }
+    s.have_frame = false;
 }
 
 int checkShape(sbm_ctx *c, int w, int h, int ch)
@@ -169,60 +193,114 @@ int checkShape(sbm_ctx *c, int w, int h, int ch)
     return 0;
 }
 
+// frame shape -> level geometry (no allocation; slots follow lazily through shape_gen)
 int ensureShape(sbm_ctx *c, int w, int h, int ch)
 {
-    if (c->w == w && c->h == h && c->c == ch && !c->lv.empty() && c->lv[0].d_quant &&
-        (!c->debug || c->lv[0].d_spread))
+    if (c->w == w && c->h == h && c->c == ch && !c->geom.empty())
         return 0;
     int rc = checkShape(c, w, h, ch);
     if (rc)
         return rc;
-    freeShape(c);
-    c->lv.resize(c->levels);
+    c->geom.assign(c->levels, LevelGeom());
     int lw = w, lh = h;
     for (int l = 0; l < c->levels; ++l)
     {
-        LevelBuf &L = c->lv[l];
+        LevelGeom &G = c->geom[l];
         if (l > 0)
             lw /= 2, lh /= 2;
-        TemplLevel *keep_tl = L.d_tl;
-        Feat *keep_f = L.d_feats;
-        L.T = c->T[l], L.w = lw, L.h = lh, L.W = lw / L.T, L.H = lh / L.T;
-        L.d_tl = keep_tl, L.d_feats = keep_f;
-        size_t px = (size_t)lw * lh;
-        if (l > 0)
-            CK(cudaMalloc(&L.d_src, px * ch));
-        CK(cudaMalloc(&L.d_quant, px));
-        L.lm_bytes = 8 * px;
-        // tail slack: flat addressing lets the last memory be over-read: a whole memory for
-        // the coarse scan past template_positions, 16 rows + 16 for the local patch, +8 for the realigning loads
-        size_t WH = (size_t)L.W * L.H;
-        L.lm_alloc = L.lm_bytes + std::max(WH, (size_t)16 * L.W + 16) + 128;
-        CK(cudaMalloc(&L.d_lm, L.lm_alloc));
-        CK(cudaMemset(L.d_lm, 0, L.lm_alloc));
-        if (c->debug)
-        {
-            CK(cudaMalloc(&L.d_spread, px));
-            CK(cudaMalloc(&L.d_resp, 8 * px));
-        }
+        G.T = c->T[l], G.w = lw, G.h = lh, G.W = lw / G.T, G.H = lh / G.T;
+        const size_t px = (size_t)lw * lh, WH = (size_t)G.W * G.H;
+        G.lm_bytes = 8 * px;
+        // tail slack: flat addressing lets the last memory be over-read: a whole memory for the
+        // coarse scan past template_positions, 16 rows + 16 for the local patch, + the realigning vector loads
+        G.lm_alloc = G.lm_bytes + std::max(WH, (size_t)16 * G.W + 16) + 128;
     }
     c->w = w, c->h = h, c->c = ch;
+    ++c->shape_gen;
     c->coarse_dirty = true;
-    c->have_frame = false;
     return 0;
+}
+
+int ensureSlot(sbm_ctx *c, Slot &s)
+{
+    if (!s.stream)
+    {
+        CK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+        for (int i = 0; i < 4; ++i)
+            CK(cudaEventCreate(&s.ev[i]));
+    }
+    if (s.shape_gen != c->shape_gen || (c->debug && !s.debug_bufs))
+    {
+        freeSlotShape(s);
+        s.lv.assign(c->levels, LevelBuf());
+        for (int l = 0; l < c->levels; ++l)
+        {
+            const LevelGeom &G = c->geom[l];
+            LevelBuf &L = s.lv[l];
+            const size_t px = (size_t)G.w * G.h;
+            if (l > 0)
+                CK(cudaMalloc(&L.d_src, px * c->c));
+            CK(cudaMalloc(&L.d_quant, px));
+            CK(cudaMalloc(&L.d_lm, G.lm_alloc));
+            CK(cudaMemset(L.d_lm, 0, G.lm_alloc));
+            if (c->debug)
+            {
+                CK(cudaMalloc(&L.d_spread, px));
+                CK(cudaMalloc(&L.d_resp, 8 * px));
+            }
+        }
+        s.shape_gen = c->shape_gen;
+        s.debug_bufs = c->debug;
+    }
+    if (!s.d_buf[0])
+    {
+        CK(cudaMalloc(&s.d_buf[0], (size_t)s.cap * sizeof(Cand)));
+        CK(cudaMalloc(&s.d_buf[1], (size_t)s.cap * sizeof(Cand)));
+    }
+    if (!s.d_counts)
+    {
+        CK(cudaMalloc(&s.d_counts, COUNT_WORDS * sizeof(uint32_t)));
+        CK(cudaMallocHost(&s.h_counts, COUNT_WORDS * sizeof(uint32_t)));
+    }
+    if (!s.h_recs)
+    {
+        s.h_recs_cap = HEAD_RECS;
+        CK(cudaMallocHost(&s.h_recs, (size_t)s.h_recs_cap * sizeof(Cand)));
+    }
+    return 0;
+}
+
+void destroySlot(Slot &s)
+{
+    freeSlotShape(s);
+    freeDev(s.d_frame);
+    freeDev(s.d_mask);
+    freeDev(s.d_buf[0]);
+    freeDev(s.d_buf[1]);
+    freeDev(s.d_counts);
+    if (s.h_counts)
+        cudaFreeHost(s.h_counts);
+    if (s.h_recs)
+        cudaFreeHost(s.h_recs);
+    for (int i = 0; i < 4; ++i)
+        if (s.ev[i])
+            cudaEventDestroy(s.ev[i]);
+    if (s.stream)
+        cudaStreamDestroy(s.stream);
+    s = Slot();
 }
 
 int ensureTemplates(sbm_ctx *c)
 {
     if (c->templates_dirty)
     {
+        CK(cudaDeviceSynchronize()); // frames in flight may still read the old arrays
         const int L = c->levels;
         c->gid_begin.assign(c->classes.size() + 1, 0);
         for (size_t k = 0; k < c->classes.size(); ++k)
             c->gid_begin[k + 1] = c->gid_begin[k] + (uint32_t)c->classes[k].n;
         c->n_templates = c->gid_begin.back();
-        if (c->lv.size() != (size_t)L)
-            c->lv.resize(L);
+        c->tl.resize(L);
         for (int l = 0; l < L; ++l)
         {
             std::vector<TemplLevel> tl(c->n_templates);
@@ -254,15 +332,15 @@ int ensureTemplates(sbm_ctx *c)
                         fo += d.num_features;
                     }
             }
-            LevelBuf &LB = c->lv[l];
-            freeDev(LB.d_tl);
-            freeDev(LB.d_feats);
-            CK(cudaMalloc(&LB.d_tl, std::max<size_t>(1, tl.size()) * sizeof(TemplLevel)));
-            CK(cudaMalloc(&LB.d_feats, std::max<size_t>(1, ff.size()) * sizeof(Feat)));
+            LevelTempl &LT = c->tl[l];
+            freeDev(LT.d_tl);
+            freeDev(LT.d_feats);
+            CK(cudaMalloc(&LT.d_tl, std::max<size_t>(1, tl.size()) * sizeof(TemplLevel)));
+            CK(cudaMalloc(&LT.d_feats, std::max<size_t>(1, ff.size()) * sizeof(Feat)));
             if (!tl.empty())
-                CK(cudaMemcpy(LB.d_tl, tl.data(), tl.size() * sizeof(TemplLevel), cudaMemcpyHostToDevice));
+                CK(cudaMemcpy(LT.d_tl, tl.data(), tl.size() * sizeof(TemplLevel), cudaMemcpyHostToDevice));
             if (!ff.empty())
-                CK(cudaMemcpy(LB.d_feats, ff.data(), ff.size() * sizeof(Feat), cudaMemcpyHostToDevice));
+                CK(cudaMemcpy(LT.d_feats, ff.data(), ff.size() * sizeof(Feat), cudaMemcpyHostToDevice));
         }
         c->templates_dirty = false;
         c->coarse_dirty = true;
@@ -273,8 +351,8 @@ int ensureTemplates(sbm_ctx *c)
         // similarity()'s per-template constants and per-feature start offsets for this frame shape
         // (line2Dup.cpp:813-838, accessLinearMemory :782-805)
         const int L = c->levels;
-        const LevelBuf &LB = c->lv[L - 1];
-        const int T = LB.T, W = LB.W, H = LB.H;
+        const LevelGeom &G = c->geom[L - 1];
+        const int T = G.T, W = G.W, H = G.H;
         const uint32_t WH = (uint32_t)W * H;
         c->h_tcoarse.assign(c->n_templates, TemplCoarse());
         std::vector<uint32_t> off;
@@ -299,7 +377,7 @@ int ensureTemplates(sbm_ctx *c)
                         for (int i = 0; i < d.num_features; ++i)
                         {
                             const sbm_feature &f = cs.feats[fo + i];
-                            if (f.x < 0 || f.x >= LB.w || f.y < 0 || f.y >= LB.h)
+                            if (f.x < 0 || f.x >= G.w || f.y < 0 || f.y >= G.h)
                                 continue;
                             if (f.label < 0 || f.label > 7)
                                 return fail(SBM_ERR_BAD_ARG, "feature label %d out of range", f.label);
@@ -313,7 +391,7 @@ int ensureTemplates(sbm_ctx *c)
                             nv += (int)cls[k].size();
                             // pad with reads of the zeroed tail (same word shift): adds 0, keeps batches full
                             while (cls[k].size() % K5_U)
-                                cls[k].push_back((uint32_t)LB.lm_bytes + 4u * k);
+                                cls[k].push_back((uint32_t)G.lm_bytes + 4u * k);
                             off.insert(off.end(), cls[k].begin(), cls[k].end());
                             stored += (int)cls[k].size();
                             o.cls_end[k] = (uint16_t)stored;
@@ -323,6 +401,7 @@ int ensureTemplates(sbm_ctx *c)
                     fo += d.num_features;
                 }
         }
+        CK(cudaDeviceSynchronize());
         freeDev(c->d_tcoarse);
         freeDev(c->d_coff);
         CK(cudaMalloc(&c->d_tcoarse, std::max<size_t>(1, c->h_tcoarse.size()) * sizeof(TemplCoarse)));
@@ -354,6 +433,8 @@ int ensureActive(sbm_ctx *c, const int *class_idx, int n_classes)
     }
     if (!c->active_dirty && req == c->active_classes)
         return 0;
+    // the previous list may still be read by frames in flight on the slot streams
+    CK(cudaDeviceSynchronize());
     c->active_classes = req;
     std::vector<int> uniq = req;
     std::sort(uniq.begin(), uniq.end());
@@ -364,8 +445,8 @@ int ensureActive(sbm_ctx *c, const int *class_idx, int n_classes)
         for (uint32_t g = c->gid_begin[k]; g < c->gid_begin[k + 1]; ++g)
         {
             act.push_back(g);
-            const TemplCoarse &t = c->h_tcoarse[g];
-            c->coarse_evals += (uint64_t)t.n_valid * (uint64_t)std::max(t.tp, 0);
+            if (g < c->h_tcoarse.size()) // empty until a frame shape is known
+                c->coarse_evals += (uint64_t)c->h_tcoarse[g].n_valid * (uint64_t)std::max(c->h_tcoarse[g].tp, 0);
         }
     freeDev(c->d_active);
     CK(cudaMalloc(&c->d_active, std::max<size_t>(1, act.size()) * sizeof(uint32_t)));
@@ -376,131 +457,128 @@ int ensureActive(sbm_ctx *c, const int *class_idx, int n_classes)
     return 0;
 }
 
-int ensureCandBuffers(sbm_ctx *c)
+// everything a match call needs before it can enqueue on slot s
+int prepare(sbm_ctx *c, Slot &s, int w, int h, int ch, const int *class_idx, int n_classes)
 {
-    if (!c->d_buf[0])
-    {
-        CK(cudaMalloc(&c->d_buf[0], (size_t)c->cap * sizeof(Cand)));
-        CK(cudaMalloc(&c->d_buf[1], (size_t)c->cap * sizeof(Cand)));
-    }
-    if (!c->d_counts)
-    {
-        CK(cudaMalloc(&c->d_counts, COUNT_WORDS * sizeof(uint32_t)));
-        CK(cudaMallocHost(&c->h_counts, COUNT_WORDS * sizeof(uint32_t)));
-    }
+    int rc;
+    if ((rc = ensureShape(c, w, h, ch)) || (rc = ensureTemplates(c)) || (rc = ensureActive(c, class_idx, n_classes)) ||
+        (rc = ensureSlot(c, s)))
+        return rc;
     return 0;
 }
 
-// Enqueue the whole pipeline for one frame resident at d_img.  user_recs/user_count: optional caller
-// buffers for the last stage.
-int enqueueFrame(sbm_ctx *c, const uint8_t *d_img, const uint8_t *d_mask, float threshold, cudaStream_t st, Cand *user_recs,
+// Enqueue the whole pipeline for one frame resident at d_img on stream st, using slot s's scratch.
+// user_recs/user_count: optional caller buffers for the last stage.
+int enqueueFrame(sbm_ctx *c, Slot &s, const uint8_t *d_img, const uint8_t *d_mask, float threshold, cudaStream_t st, Cand *user_recs,
                  uint32_t user_cap, uint32_t *user_count)
 {
     const int L = c->levels;
     int launches = 0;
-    CK(cudaMemsetAsync(c->d_counts, 0, COUNT_WORDS * sizeof(uint32_t), st));
+    CK(cudaMemsetAsync(s.d_counts, 0, COUNT_WORDS * sizeof(uint32_t), st));
     if (user_count)
         CK(cudaMemsetAsync(user_count, 0, 2 * sizeof(uint32_t), st));
     if (c->timing)
-        CK(cudaEventRecord(c->ev[0], st));
+        CK(cudaEventRecord(s.ev[0], st));
     const float weak_sq = c->weak * c->weak;
     const uint8_t *src = d_img;
     for (int l = 0; l < L; ++l)
     {
-        LevelBuf &LB = c->lv[l];
+        const LevelGeom &G = c->geom[l];
+        LevelBuf &LB = s.lv[l];
         if (l > 0)
         {
-            const LevelBuf &P = c->lv[l - 1];
-            dim3 g((LB.w + 31) / 32, (LB.h + 7) / 8);
+            const LevelGeom &P = c->geom[l - 1];
+            dim3 g((G.w + 31) / 32, (G.h + 7) / 8);
             if (c->c == 3)
-                k_pyrdown<3><<<g, 256, 0, st>>>(src, P.w, P.h, LB.d_src, LB.w, LB.h);
+                k_pyrdown<3><<<g, 256, 0, st>>>(src, P.w, P.h, LB.d_src, G.w, G.h);
             else
-                k_pyrdown<1><<<g, 256, 0, st>>>(src, P.w, P.h, LB.d_src, LB.w, LB.h);
+                k_pyrdown<1><<<g, 256, 0, st>>>(src, P.w, P.h, LB.d_src, G.w, G.h);
             src = LB.d_src;
             ++launches;
         }
         // 64x32 tiles unless that leaves the GPU under two waves of CTAs; then 64x16
-        const bool tall = ((LB.w + K1_TW - 1) / K1_TW) * ((LB.h + 31) / 32) >= 2 * 148;
+        const bool tall = ((G.w + K1_TW - 1) / K1_TW) * ((G.h + 31) / 32) >= 2 * 148;
         const int th = tall ? 32 : 16;
-        dim3 g1((LB.w + K1_TW - 1) / K1_TW, (LB.h + th - 1) / th);
+        dim3 g1((G.w + K1_TW - 1) / K1_TW, (G.h + th - 1) / th);
         if (c->c == 3 && tall)
-            k_orient<3, 32><<<g1, K1_THREADS, 0, st>>>(src, LB.w, LB.h, d_mask, l, c->w, weak_sq, LB.d_quant);
+            k_orient<3, 32><<<g1, K1_THREADS, 0, st>>>(src, G.w, G.h, d_mask, l, c->w, weak_sq, LB.d_quant);
         else if (c->c == 3)
-            k_orient<3, 16><<<g1, K1_THREADS, 0, st>>>(src, LB.w, LB.h, d_mask, l, c->w, weak_sq, LB.d_quant);
+            k_orient<3, 16><<<g1, K1_THREADS, 0, st>>>(src, G.w, G.h, d_mask, l, c->w, weak_sq, LB.d_quant);
         else if (tall)
-            k_orient<1, 32><<<g1, K1_THREADS, 0, st>>>(src, LB.w, LB.h, d_mask, l, c->w, weak_sq, LB.d_quant);
+            k_orient<1, 32><<<g1, K1_THREADS, 0, st>>>(src, G.w, G.h, d_mask, l, c->w, weak_sq, LB.d_quant);
         else
-            k_orient<1, 16><<<g1, K1_THREADS, 0, st>>>(src, LB.w, LB.h, d_mask, l, c->w, weak_sq, LB.d_quant);
-        dim3 g2((LB.w + K2_PW - 1) / K2_PW, (LB.h + K2_PH - 1) / K2_PH);
+            k_orient<1, 16><<<g1, K1_THREADS, 0, st>>>(src, G.w, G.h, d_mask, l, c->w, weak_sq, LB.d_quant);
+        dim3 g2((G.w + K2_PW - 1) / K2_PW, (G.h + K2_PH - 1) / K2_PH);
         uint8_t *ds = c->debug ? LB.d_spread : nullptr, *dr = c->debug ? LB.d_resp : nullptr;
-        if (LB.T == 4)
-            k_spread_linearize<4><<<g2, K2_THREADS, 0, st>>>(LB.d_quant, LB.w, LB.h, LB.d_lm, ds, dr);
-        else if (LB.T == 8)
-            k_spread_linearize<8><<<g2, K2_THREADS, 0, st>>>(LB.d_quant, LB.w, LB.h, LB.d_lm, ds, dr);
-        else if (LB.T == 2)
-            k_spread_linearize<2><<<g2, K2_THREADS, 0, st>>>(LB.d_quant, LB.w, LB.h, LB.d_lm, ds, dr);
+        if (G.T == 4)
+            k_spread_linearize<4><<<g2, K2_THREADS, 0, st>>>(LB.d_quant, G.w, G.h, LB.d_lm, ds, dr);
+        else if (G.T == 8)
+            k_spread_linearize<8><<<g2, K2_THREADS, 0, st>>>(LB.d_quant, G.w, G.h, LB.d_lm, ds, dr);
+        else if (G.T == 2)
+            k_spread_linearize<2><<<g2, K2_THREADS, 0, st>>>(LB.d_quant, G.w, G.h, LB.d_lm, ds, dr);
         else
-            k_spread_linearize<16><<<g2, K2_THREADS, 0, st>>>(LB.d_quant, LB.w, LB.h, LB.d_lm, ds, dr);
+            k_spread_linearize<16><<<g2, K2_THREADS, 0, st>>>(LB.d_quant, G.w, G.h, LB.d_lm, ds, dr);
         launches += 2;
     }
     if (c->timing)
-        CK(cudaEventRecord(c->ev[1], st));
+        CK(cudaEventRecord(s.ev[1], st));
 
     // coarse similarity + threshold at the last level
-    const LevelBuf &CL = c->lv[L - 1];
-    const int HW = CL.W * CL.H;
-    Cand *out = (L == 1 && user_recs) ? user_recs : c->d_buf[0];
-    uint32_t out_cap = (L == 1 && user_recs) ? user_cap : c->cap;
-    uint32_t *out_cnt = (L == 1 && user_count) ? user_count : c->d_counts + 0;
+    const LevelGeom &CG = c->geom[L - 1];
+    const int HW = CG.W * CG.H;
+    Cand *out = (L == 1 && user_recs) ? user_recs : s.d_buf[0];
+    uint32_t out_cap = (L == 1 && user_recs) ? user_cap : s.cap;
+    uint32_t *out_cnt = (L == 1 && user_count) ? user_count : s.d_counts + 0;
     if (c->n_active > 0)
     {
         dim3 g(c->n_active, (HW + K5_TILE - 1) / K5_TILE);
-        k_similarity<<<g, K5_THREADS, 0, st>>>(CL.d_lm, c->d_coff, c->d_tcoarse, c->d_active, CL.W, HW, CL.T, threshold, out,
+        k_similarity<<<g, K5_THREADS, 0, st>>>(s.lv[L - 1].d_lm, c->d_coff, c->d_tcoarse, c->d_active, CG.W, HW, CG.T, threshold, out,
                                                out_cnt, out_cap, nullptr);
         ++launches;
     }
     if (c->timing)
-        CK(cudaEventRecord(c->ev[3], st));
+        CK(cudaEventRecord(s.ev[3], st));
     Cand *in = out;
     uint32_t in_cap = out_cap;
     uint32_t *in_cnt = out_cnt;
     int stage = 1;
     for (int l = L - 2; l >= 0; --l, ++stage)
     {
-        const LevelBuf &LB = c->lv[l];
+        const LevelGeom &G = c->geom[l];
         bool last = (l == 0);
-        out = (last && user_recs) ? user_recs : c->d_buf[stage & 1];
-        out_cap = (last && user_recs) ? user_cap : c->cap;
-        out_cnt = (last && user_count) ? user_count : c->d_counts + stage;
+        out = (last && user_recs) ? user_recs : s.d_buf[stage & 1];
+        out_cap = (last && user_recs) ? user_cap : s.cap;
+        out_cnt = (last && user_count) ? user_count : s.d_counts + stage;
         if (c->n_active > 0)
         {
-            k_refine<<<148 * 4, K6_THREADS, 0, st>>>(LB.d_lm, LB.d_tl, LB.d_feats, in, in_cnt, in_cap, out, out_cnt, out_cap, LB.w,
-                                                     LB.h, LB.T, threshold, nullptr, 0,
-                                                     reinterpret_cast<unsigned long long *>(c->d_counts + 10));
+            k_refine<<<148 * 4, K6_THREADS, 0, st>>>(s.lv[l].d_lm, c->tl[l].d_tl, c->tl[l].d_feats, in, in_cnt, in_cap, out, out_cnt, out_cap,
+                                                     G.w, G.h, G.T, threshold, nullptr, 0,
+                                                     reinterpret_cast<unsigned long long *>(s.d_counts + 10));
             ++launches;
         }
         in = out, in_cap = out_cap, in_cnt = out_cnt;
     }
     if (c->timing)
-        CK(cudaEventRecord(c->ev[2], st));
-    c->d_final = in;
-    c->d_final_count = in_cnt;
-    c->final_cap = in_cap;
-    c->launches = launches;
+        CK(cudaEventRecord(s.ev[2], st));
+    s.d_final = in;
+    s.d_final_count = in_cnt;
+    s.final_cap = in_cap;
+    s.launches = launches;
     CK(cudaGetLastError());
-    c->have_frame = true;
+    s.have_frame = true;
     return 0;
 }
 
-int growCap(sbm_ctx *c, uint32_t need)
+int growCap(sbm_ctx *c, Slot &s, uint32_t need)
 {
-    uint32_t nc = c->cap;
+    uint32_t nc = s.cap;
     while (nc < need)
         nc *= 2;
-    freeDev(c->d_buf[0]);
-    freeDev(c->d_buf[1]);
-    c->cap = nc;
-    return ensureCandBuffers(c);
+    CK(cudaStreamSynchronize(s.stream));
+    freeDev(s.d_buf[0]);
+    freeDev(s.d_buf[1]);
+    s.cap = nc;
+    return ensureSlot(c, s);
 }
 
 // (class occurrence order, template_id, coarse scan index) -> reference's serial candidate order
@@ -546,36 +624,81 @@ int orderRecords(sbm_ctx *c, const Cand *recs, uint32_t n, bool finalize, sbm_ma
     return 0;
 }
 
-int fetchRecords(sbm_ctx *c, cudaStream_t st, uint32_t *n_out)
+// queue the D2H of the counters and the head of the record buffer behind the frame's kernels
+int enqueueFetch(Slot &s, cudaStream_t st)
 {
-    if (!c->h_recs)
-    {
-        c->h_recs_cap = std::max(c->cap, HEAD_RECS);
-        CK(cudaMallocHost(&c->h_recs, (size_t)c->h_recs_cap * sizeof(Cand)));
-    }
-    // one round trip for the common case: counters + the first HEAD_RECS records together
-    uint32_t head = std::min(HEAD_RECS, c->final_cap);
-    CK(cudaMemcpyAsync(c->h_counts, c->d_counts, COUNT_WORDS * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
-    CK(cudaMemcpyAsync(c->h_recs, c->d_final, (size_t)head * sizeof(Cand), cudaMemcpyDeviceToHost, st));
+    const uint32_t head = std::min(HEAD_RECS, s.final_cap);
+    CK(cudaMemcpyAsync(s.h_counts, s.d_counts, COUNT_WORDS * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(s.h_recs, s.d_final, (size_t)head * sizeof(Cand), cudaMemcpyDeviceToHost, st));
+    return 0;
+}
+
+// wait for the slot's frame; returns SBM_ERR_CAPACITY (without error text) when a stage overflowed
+int finishFetch(sbm_ctx *c, Slot &s, cudaStream_t st, uint32_t *n_out)
+{
     CK(cudaStreamSynchronize(st));
-    uint32_t n = c->h_counts[c->d_final_count - c->d_counts];
+    const uint32_t n = s.h_counts[s.d_final_count - s.d_counts];
     *n_out = n;
-    for (int s = 0; s < c->levels; ++s)
-        if (c->h_counts[s] > c->cap)
+    for (int k = 0; k < c->levels; ++k)
+        if (s.h_counts[k] > s.cap)
             return SBM_ERR_CAPACITY;
+    uint32_t head = std::min(HEAD_RECS, s.final_cap);
     if (n > head)
     {
-        if (n > c->h_recs_cap)
+        if (n > s.h_recs_cap)
         {
-            cudaFreeHost(c->h_recs);
-            c->h_recs_cap = n;
-            CK(cudaMallocHost(&c->h_recs, (size_t)n * sizeof(Cand)));
+            cudaFreeHost(s.h_recs);
+            s.h_recs = nullptr;
+            s.h_recs_cap = n;
+            CK(cudaMallocHost(&s.h_recs, (size_t)n * sizeof(Cand)));
             head = 0;
         }
-        CK(cudaMemcpyAsync(c->h_recs + head, c->d_final + head, (size_t)(n - head) * sizeof(Cand), cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(s.h_recs + head, s.d_final + head, (size_t)(n - head) * sizeof(Cand), cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));
     }
     return 0;
+}
+
+int uploadFrame(Slot &s, const uint8_t *img, int w, int h, int ch, size_t stride, const uint8_t *mask, const uint8_t **d_mask_out)
+{
+    cudaStream_t st = s.stream;
+    const size_t row = (size_t)w * ch, bytes = row * h;
+    if (s.frame_alloc < bytes)
+    {
+        CK(cudaStreamSynchronize(st));
+        freeDev(s.d_frame);
+        CK(cudaMalloc(&s.d_frame, bytes));
+        s.frame_alloc = bytes;
+    }
+    if (stride == 0 || stride == row)
+        CK(cudaMemcpyAsync(s.d_frame, img, bytes, cudaMemcpyHostToDevice, st));
+    else
+        CK(cudaMemcpy2DAsync(s.d_frame, row, img, stride, row, h, cudaMemcpyHostToDevice, st));
+    *d_mask_out = nullptr;
+    if (mask)
+    {
+        const size_t mb = (size_t)w * h;
+        if (s.mask_alloc < mb)
+        {
+            CK(cudaStreamSynchronize(st));
+            freeDev(s.d_mask);
+            CK(cudaMalloc(&s.d_mask, mb));
+            s.mask_alloc = mb;
+        }
+        CK(cudaMemcpyAsync(s.d_mask, mask, mb, cudaMemcpyHostToDevice, st));
+        *d_mask_out = s.d_mask;
+    }
+    s.last_src0 = s.d_frame;
+    return 0;
+}
+
+void recordStats(sbm_ctx *c, const Slot &s, uint32_t n)
+{
+    c->stats[0] = c->coarse_evals;
+    c->stats[1] = s.h_counts[0];
+    memcpy(&c->stats[2], &s.h_counts[10], sizeof(uint64_t));
+    c->stats[3] = n;
+    c->stats[4] = (uint64_t)s.launches;
 }
 
 int matchHost(sbm_ctx *c, const uint8_t *img, int w, int h, int ch, size_t stride, const uint8_t *mask, float threshold,
@@ -585,59 +708,66 @@ int matchHost(sbm_ctx *c, const uint8_t *img, int w, int h, int ch, size_t strid
         return fail(SBM_ERR_BAD_ARG, "null argument");
     std::lock_guard<std::mutex> lock(c->mu);
     CK(cudaSetDevice(c->device));
+    Slot &s = c->slot[0];
     int rc;
-    if ((rc = ensureShape(c, w, h, ch)) || (rc = ensureTemplates(c)) || (rc = ensureActive(c, class_idx, n_classes)) ||
-        (rc = ensureCandBuffers(c)))
+    if ((rc = prepare(c, s, w, h, ch, class_idx, n_classes)))
         return rc;
-    cudaStream_t st = c->own_stream;
-    size_t row = (size_t)w * ch, bytes = row * h;
-    if (c->frame_alloc < bytes)
-    {
-        freeDev(c->d_frame);
-        CK(cudaMalloc(&c->d_frame, bytes));
-        c->frame_alloc = bytes;
-    }
-    if (stride == 0 || stride == row)
-        CK(cudaMemcpyAsync(c->d_frame, img, bytes, cudaMemcpyHostToDevice, st));
-    else
-        CK(cudaMemcpy2DAsync(c->d_frame, row, img, stride, row, h, cudaMemcpyHostToDevice, st));
     const uint8_t *dm = nullptr;
-    if (mask)
-    {
-        size_t mb = (size_t)w * h;
-        if (c->mask_alloc < mb)
-        {
-            freeDev(c->d_mask);
-            CK(cudaMalloc(&c->d_mask, mb));
-            c->mask_alloc = mb;
-        }
-        CK(cudaMemcpyAsync(c->d_mask, mask, mb, cudaMemcpyHostToDevice, st));
-        dm = c->d_mask;
-    }
-    c->last_src0 = c->d_frame;
+    if ((rc = uploadFrame(s, img, w, h, ch, stride, mask, &dm)))
+        return rc;
     for (int attempt = 0; attempt < 8; ++attempt)
     {
-        if ((rc = enqueueFrame(c, c->d_frame, dm, threshold, st, nullptr, 0, nullptr)))
+        if ((rc = enqueueFrame(c, s, s.d_frame, dm, threshold, s.stream, nullptr, 0, nullptr)) || (rc = enqueueFetch(s, s.stream)))
             return rc;
         uint32_t n = 0;
-        rc = fetchRecords(c, st, &n);
+        rc = finishFetch(c, s, s.stream, &n);
         if (rc == SBM_ERR_CAPACITY)
         {
             uint32_t need = 0;
-            for (int s = 0; s < c->levels; ++s)
-                need = std::max(need, c->h_counts[s]);
-            if ((rc = growCap(c, need)))
+            for (int k = 0; k < c->levels; ++k)
+                need = std::max(need, s.h_counts[k]);
+            if ((rc = growCap(c, s, need)))
                 return rc;
             continue;
         }
         if (rc)
             return rc;
-        c->stats[0] = c->coarse_evals;
-        c->stats[1] = c->h_counts[0];
-        memcpy(&c->stats[2], &c->h_counts[10], sizeof(uint64_t));
-        c->stats[3] = n;
-        c->stats[4] = (uint64_t)c->launches;
-        return orderRecords(c, c->h_recs, n, finalize, out, cap, n_out);
+        recordStats(c, s, n);
+        return orderRecords(c, s.h_recs, n, finalize, out, cap, n_out);
+    }
+    return fail(SBM_ERR_CAPACITY, "candidate buffers keep overflowing");
+}
+
+// finish the frame in flight on slot s (re-running it with larger buffers if a stage overflowed) and append its
+// ordered records to out[*used ..)
+int finishBatchFrame(sbm_ctx *c, Slot &s, const uint8_t *dm, float threshold, bool finalize, sbm_match_rec *out, int cap, int *used,
+                     bool *overflowed)
+{
+    int rc;
+    for (int attempt = 0; attempt < 8; ++attempt)
+    {
+        uint32_t n = 0;
+        rc = finishFetch(c, s, s.stream, &n);
+        if (rc == SBM_ERR_CAPACITY)
+        {
+            uint32_t need = 0;
+            for (int k = 0; k < c->levels; ++k)
+                need = std::max(need, s.h_counts[k]);
+            if ((rc = growCap(c, s, need)) || (rc = enqueueFrame(c, s, s.d_frame, dm, threshold, s.stream, nullptr, 0, nullptr)) ||
+                (rc = enqueueFetch(s, s.stream)))
+                return rc;
+            continue;
+        }
+        if (rc)
+            return rc;
+        recordStats(c, s, n);
+        int got = 0;
+        const int room = *overflowed ? 0 : std::max(0, cap - *used);
+        rc = orderRecords(c, s.h_recs, n, finalize, out ? out + *used : nullptr, room, &got);
+        if (rc == SBM_ERR_CAPACITY)
+            *overflowed = true, rc = 0;
+        *used += got;
+        return rc;
     }
     return fail(SBM_ERR_CAPACITY, "candidate buffers keep overflowing");
 }
@@ -674,10 +804,7 @@ int sbm_create(const int *T, int levels, float weak, float strong, int num_featu
     c->T.assign(T, T + levels);
     c->levels = levels;
     c->weak = weak, c->strong = strong, c->num_features = num_features;
-    c->lv.resize(levels);
-    CK(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
-    for (int i = 0; i < 4; ++i)
-        CK(cudaEventCreate(&c->ev[i]));
+    c->tl.resize(levels);
     *out = c;
     return 0;
 }
@@ -688,29 +815,16 @@ int sbm_destroy(sbm_ctx *c)
         return 0;
     cudaSetDevice(c->device);
     cudaDeviceSynchronize();
-    freeShape(c);
-    for (auto &l : c->lv)
+    for (auto &s : c->slot)
+        destroySlot(s);
+    for (auto &l : c->tl)
     {
         freeDev(l.d_tl);
         freeDev(l.d_feats);
     }
-    freeDev(c->d_frame);
-    freeDev(c->d_mask);
     freeDev(c->d_tcoarse);
     freeDev(c->d_coff);
     freeDev(c->d_active);
-    freeDev(c->d_buf[0]);
-    freeDev(c->d_buf[1]);
-    freeDev(c->d_counts);
-    if (c->h_counts)
-        cudaFreeHost(c->h_counts);
-    if (c->h_recs)
-        cudaFreeHost(c->h_recs);
-    for (int i = 0; i < 4; ++i)
-        if (c->ev[i])
-            cudaEventDestroy(c->ev[i]);
-    if (c->own_stream)
-        cudaStreamDestroy(c->own_stream);
     delete c;
     return 0;
 }
@@ -775,6 +889,50 @@ int sbm_match_candidates(sbm_ctx *c, const uint8_t *img, int w, int h, int ch, s
     return matchHost(c, img, w, h, ch, stride, mask, threshold, class_idx, n_classes, false, out, cap, n_out);
 }
 
+int sbm_match_batch(sbm_ctx *c, const uint8_t *const *imgs, const uint8_t *const *masks, int n_frames, int w, int h, int ch,
+                    size_t stride, float threshold, const int *class_idx, int n_classes, sbm_match_rec *out, int cap,
+                    int *frame_begin)
+{
+    if (!c || !imgs || n_frames < 0 || !frame_begin)
+        return fail(SBM_ERR_BAD_ARG, "null argument");
+    for (int i = 0; i < n_frames; ++i)
+        if (!imgs[i])
+            return fail(SBM_ERR_BAD_ARG, "frame %d is null", i);
+    std::lock_guard<std::mutex> lock(c->mu);
+    CK(cudaSetDevice(c->device));
+    int rc;
+    frame_begin[0] = 0;
+    if (n_frames == 0)
+        return 0;
+    for (int k = 0; k < std::min(n_frames, SBM_SLOTS); ++k)
+        if ((rc = prepare(c, c->slot[k], w, h, ch, class_idx, n_classes)))
+            return rc;
+    const uint8_t *dm[SBM_SLOTS] = {nullptr};
+    int used = 0;
+    bool overflowed = false;
+    for (int i = 0; i < n_frames + SBM_SLOTS; ++i)
+    {
+        const int done = i - SBM_SLOTS; // the frame that occupied this slot before
+        Slot &s = c->slot[i % SBM_SLOTS];
+        if (done >= 0 && done < n_frames)
+        {
+            if ((rc = finishBatchFrame(c, s, dm[i % SBM_SLOTS], threshold, true, out, cap, &used, &overflowed)))
+                return rc;
+            frame_begin[done + 1] = used;
+        }
+        if (i < n_frames)
+        {
+            if ((rc = uploadFrame(s, imgs[i], w, h, ch, stride, masks ? masks[i] : nullptr, &dm[i % SBM_SLOTS])) ||
+                (rc = enqueueFrame(c, s, s.d_frame, dm[i % SBM_SLOTS], threshold, s.stream, nullptr, 0, nullptr)) ||
+                (rc = enqueueFetch(s, s.stream)))
+                return rc;
+        }
+    }
+    if (overflowed)
+        return fail(SBM_ERR_CAPACITY, "output holds %d matches, %d needed", cap, used);
+    return 0;
+}
+
 int sbm_match_device(sbm_ctx *c, const void *d_img, int w, int h, int ch, const void *d_mask, float threshold,
                      const int *class_idx, int n_classes, void *d_records, int cap, void *d_count, void *stream)
 {
@@ -782,26 +940,73 @@ int sbm_match_device(sbm_ctx *c, const void *d_img, int w, int h, int ch, const 
         return fail(SBM_ERR_BAD_ARG, "null argument");
     std::lock_guard<std::mutex> lock(c->mu);
     CK(cudaSetDevice(c->device));
+    Slot &s = c->slot[0];
     int rc;
-    if ((rc = ensureShape(c, w, h, ch)) || (rc = ensureTemplates(c)) || (rc = ensureActive(c, class_idx, n_classes)) ||
-        (rc = ensureCandBuffers(c)))
+    if ((rc = prepare(c, s, w, h, ch, class_idx, n_classes)))
         return rc;
-    cudaStream_t st = stream ? (cudaStream_t)stream : c->own_stream;
-    c->last_src0 = (const uint8_t *)d_img;
-    return enqueueFrame(c, (const uint8_t *)d_img, (const uint8_t *)d_mask, threshold, st, (Cand *)d_records,
+    cudaStream_t st = stream ? (cudaStream_t)stream : s.stream;
+    s.last_src0 = (const uint8_t *)d_img;
+    return enqueueFrame(c, s, (const uint8_t *)d_img, (const uint8_t *)d_mask, threshold, st, (Cand *)d_records,
                         d_records ? (uint32_t)cap : 0, (uint32_t *)d_count);
+}
+
+int sbm_match_batch_device(sbm_ctx *c, const void *d_imgs, size_t frame_stride, int n_frames, int w, int h, int ch, float threshold,
+                           const int *class_idx, int n_classes, void *d_records, int cap_per_frame, void *d_counts, void *stream)
+{
+    if (!c || !d_imgs || n_frames < 0 || !d_records || !d_counts || cap_per_frame <= 0)
+        return fail(SBM_ERR_BAD_ARG, "bad argument");
+    std::lock_guard<std::mutex> lock(c->mu);
+    CK(cudaSetDevice(c->device));
+    int rc;
+    const int ns = std::min(n_frames, SBM_SLOTS);
+    for (int k = 0; k < ns; ++k)
+        if ((rc = prepare(c, c->slot[k], w, h, ch, class_idx, n_classes)))
+            return rc;
+    cudaStream_t user = (cudaStream_t)stream;
+    // fork: every slot stream starts after the work already queued on the caller's stream
+    Slot &s0 = c->slot[0];
+    if (ns > 0)
+    {
+        CK(cudaEventRecord(s0.ev[0], user));
+        for (int k = 0; k < ns; ++k)
+            CK(cudaStreamWaitEvent(c->slot[k].stream, s0.ev[0], 0));
+    }
+    const bool timing = c->timing;
+    c->timing = false; // the per-stage events belong to the single-frame path
+    for (int i = 0; i < n_frames; ++i)
+    {
+        Slot &s = c->slot[i % SBM_SLOTS];
+        const uint8_t *img = (const uint8_t *)d_imgs + (size_t)i * frame_stride;
+        s.last_src0 = img;
+        rc = enqueueFrame(c, s, img, nullptr, threshold, s.stream, (Cand *)d_records + (size_t)i * cap_per_frame, (uint32_t)cap_per_frame,
+                          (uint32_t *)d_counts + 2 * (size_t)i);
+        if (rc)
+        {
+            c->timing = timing;
+            return rc;
+        }
+    }
+    c->timing = timing;
+    // join: the caller's stream continues after the last frame of every slot
+    for (int k = 0; k < ns; ++k)
+    {
+        CK(cudaEventRecord(c->slot[k].ev[1], c->slot[k].stream));
+        CK(cudaStreamWaitEvent(user, c->slot[k].ev[1], 0));
+    }
+    return 0;
 }
 
 int sbm_device_results(sbm_ctx *c, void **d_records, void **d_count, int *cap)
 {
-    if (!c || !c->have_frame)
+    if (!c || !c->slot[0].have_frame)
         return fail(SBM_ERR_STATE, "no frame has been processed");
+    const Slot &s = c->slot[0];
     if (d_records)
-        *d_records = c->d_final;
+        *d_records = s.d_final;
     if (d_count)
-        *d_count = c->d_final_count;
+        *d_count = s.d_final_count;
     if (cap)
-        *cap = (int)c->final_cap;
+        *cap = (int)s.final_cap;
     return 0;
 }
 
@@ -839,11 +1044,13 @@ int sbm_get_intermediate(sbm_ctx *c, int level, int kind, void *dst, size_t byte
     if (!c || level < 0 || level >= c->levels)
         return fail(SBM_ERR_BAD_ARG, "bad level");
     std::lock_guard<std::mutex> lock(c->mu);
-    if (!c->have_frame)
+    const Slot &s = c->slot[0];
+    if (!s.have_frame)
         return fail(SBM_ERR_STATE, "no frame has been processed");
     CK(cudaSetDevice(c->device));
-    const LevelBuf &L = c->lv[level];
-    size_t px = (size_t)L.w * L.h, need = 0;
+    const LevelGeom &G = c->geom[level];
+    const LevelBuf &L = s.lv[level];
+    size_t px = (size_t)G.w * G.h, need = 0;
     const void *src = nullptr;
     switch (kind)
     {
@@ -851,7 +1058,7 @@ int sbm_get_intermediate(sbm_ctx *c, int level, int kind, void *dst, size_t byte
     case SBM_SPREAD: need = px, src = L.d_spread; break;
     case SBM_RESPONSE: need = 8 * px, src = L.d_resp; break;
     case SBM_LINEAR: need = 8 * px, src = L.d_lm; break;
-    case SBM_PYRAMID_SRC: need = px * c->c, src = level == 0 ? c->last_src0 : L.d_src; break;
+    case SBM_PYRAMID_SRC: need = px * c->c, src = level == 0 ? s.last_src0 : L.d_src; break;
     default: return fail(SBM_ERR_BAD_ARG, "unknown intermediate kind %d", kind);
     }
     if (bytes_needed)
@@ -872,13 +1079,14 @@ int sbm_similarity_map(sbm_ctx *c, int class_idx, int template_id, uint16_t *dst
     if (!c || !dst)
         return fail(SBM_ERR_BAD_ARG, "null argument");
     std::lock_guard<std::mutex> lock(c->mu);
-    if (!c->have_frame)
+    Slot &s = c->slot[0];
+    if (!s.have_frame)
         return fail(SBM_ERR_STATE, "no frame has been processed");
     if (class_idx < 0 || (size_t)class_idx >= c->classes.size() || template_id < 0 || template_id >= c->classes[class_idx].n)
         return fail(SBM_ERR_BAD_ARG, "unknown class/template"); // CV_Assert in getTemplates (line2Dup.cpp:1454-1456)
     CK(cudaSetDevice(c->device));
-    const LevelBuf &CL = c->lv[c->levels - 1];
-    const int HW = CL.W * CL.H;
+    const LevelGeom &CG = c->geom[c->levels - 1];
+    const int HW = CG.W * CG.H;
     if (bytes != (size_t)HW * 2)
         return fail(SBM_ERR_BAD_ARG, "buffer holds %zu bytes, %d needed", bytes, HW * 2);
     uint32_t gid = c->gid_begin[class_idx] + template_id;
@@ -892,9 +1100,9 @@ int sbm_similarity_map(sbm_ctx *c, int class_idx, int template_id, uint16_t *dst
     CK(cudaMemcpy(d_one, &gid, 4, cudaMemcpyHostToDevice));
     CK(cudaMemset(d_cnt, 0, 4));
     dim3 g(1, (HW + K5_TILE - 1) / K5_TILE);
-    k_similarity<<<g, K5_THREADS, 0, c->own_stream>>>(CL.d_lm, c->d_coff, c->d_tcoarse, d_one, CL.W, HW, CL.T, 1e30f, d_sink, d_cnt, 0,
-                                                      d_dump);
-    CK(cudaStreamSynchronize(c->own_stream));
+    k_similarity<<<g, K5_THREADS, 0, s.stream>>>(s.lv[c->levels - 1].d_lm, c->d_coff, c->d_tcoarse, d_one, CG.W, HW, CG.T, 1e30f, d_sink,
+                                                 d_cnt, 0, d_dump);
+    CK(cudaStreamSynchronize(s.stream));
     CK(cudaMemcpy(dst, d_dump, (size_t)HW * 2, cudaMemcpyDeviceToHost));
     cudaFree(d_one), cudaFree(d_cnt), cudaFree(d_sink), cudaFree(d_dump);
     return 0;
@@ -905,12 +1113,13 @@ int sbm_similarity_local(sbm_ctx *c, int class_idx, int template_id, int level, 
     if (!c || !dst || level < 0 || level >= c->levels)
         return fail(SBM_ERR_BAD_ARG, "bad argument");
     std::lock_guard<std::mutex> lock(c->mu);
-    if (!c->have_frame)
+    Slot &s = c->slot[0];
+    if (!s.have_frame)
         return fail(SBM_ERR_STATE, "no frame has been processed");
     if (class_idx < 0 || (size_t)class_idx >= c->classes.size() || template_id < 0 || template_id >= c->classes[class_idx].n)
         return fail(SBM_ERR_BAD_ARG, "unknown class/template");
     CK(cudaSetDevice(c->device));
-    const LevelBuf &LB = c->lv[level];
+    const LevelGeom &G = c->geom[level];
     Cand one;
     one.x = x, one.y = y, one.sim = 0, one.tgid = c->gid_begin[class_idx] + template_id, one.key = 0;
     Cand *d_in = nullptr, *d_out = nullptr;
@@ -926,9 +1135,9 @@ int sbm_similarity_local(sbm_ctx *c, int class_idx, int template_id, int level, 
     CK(cudaMemcpy(d_in, &one, sizeof(Cand), cudaMemcpyHostToDevice));
     CK(cudaMemcpy(d_cnt, cnt, 8, cudaMemcpyHostToDevice));
     CK(cudaMemset(d_ev, 0, 8));
-    k_refine<<<1, K6_THREADS, 0, c->own_stream>>>(LB.d_lm, LB.d_tl, LB.d_feats, d_in, d_cnt, 1, d_out, d_cnt + 1, 1, LB.w, LB.h, LB.T,
-                                                  1e30f, d_dump, 1, d_ev);
-    CK(cudaStreamSynchronize(c->own_stream));
+    k_refine<<<1, K6_THREADS, 0, s.stream>>>(s.lv[level].d_lm, c->tl[level].d_tl, c->tl[level].d_feats, d_in, d_cnt, 1, d_out, d_cnt + 1, 1,
+                                             G.w, G.h, G.T, 1e30f, d_dump, 1, d_ev);
+    CK(cudaStreamSynchronize(s.stream));
     CK(cudaMemcpy(dst, d_dump, 512, cudaMemcpyDeviceToHost));
     cudaFree(d_in), cudaFree(d_out), cudaFree(d_cnt), cudaFree(d_ev), cudaFree(d_dump);
     return 0;
@@ -940,7 +1149,7 @@ int sbm_last_stats(sbm_ctx *c, uint64_t stats[8])
         return fail(SBM_ERR_BAD_ARG, "null argument");
     memcpy(stats, c->stats, sizeof(c->stats));
     stats[0] = c->coarse_evals;
-    stats[4] = (uint64_t)c->launches;
+    stats[4] = (uint64_t)c->slot[0].launches;
     return 0;
 }
 
@@ -948,16 +1157,47 @@ int sbm_last_timing(sbm_ctx *c, float ms[4])
 {
     if (!c || !ms)
         return fail(SBM_ERR_BAD_ARG, "null argument");
-    if (c->timing && c->have_frame)
+    Slot &s = c->slot[0];
+    if (c->timing && s.have_frame)
     {
         CK(cudaSetDevice(c->device));
-        CK(cudaEventSynchronize(c->ev[2]));
-        cudaEventElapsedTime(&c->last_ms[0], c->ev[0], c->ev[2]);
-        cudaEventElapsedTime(&c->last_ms[1], c->ev[0], c->ev[1]);
-        cudaEventElapsedTime(&c->last_ms[2], c->ev[1], c->ev[3]);
-        cudaEventElapsedTime(&c->last_ms[3], c->ev[3], c->ev[2]);
+        CK(cudaEventSynchronize(s.ev[2]));
+        cudaEventElapsedTime(&c->last_ms[0], s.ev[0], s.ev[2]);
+        cudaEventElapsedTime(&c->last_ms[1], s.ev[0], s.ev[1]);
+        cudaEventElapsedTime(&c->last_ms[2], s.ev[1], s.ev[3]);
+        cudaEventElapsedTime(&c->last_ms[3], s.ev[3], s.ev[2]);
     }
     memcpy(ms, c->last_ms, sizeof(c->last_ms));
+    return 0;
+}
+
+int sbm_time_similarity(sbm_ctx *c, float threshold, int iters, float *ms_per_launch)
+{
+    if (!c || !ms_per_launch || iters < 1)
+        return fail(SBM_ERR_BAD_ARG, "bad argument");
+    std::lock_guard<std::mutex> lock(c->mu);
+    Slot &s = c->slot[0];
+    if (!s.have_frame || c->n_active == 0)
+        return fail(SBM_ERR_STATE, "no frame has been processed");
+    CK(cudaSetDevice(c->device));
+    const int L = c->levels;
+    const LevelGeom &CG = c->geom[L - 1];
+    const int HW = CG.W * CG.H;
+    dim3 g(c->n_active, (HW + K5_TILE - 1) / K5_TILE);
+    CK(cudaStreamSynchronize(s.stream));
+    for (int i = 0; i < iters + 3; ++i)
+    {
+        if (i == 3)
+            CK(cudaEventRecord(s.ev[0], s.stream));
+        // same launch as the pipeline's; the candidate counter keeps running, records beyond cap are dropped
+        k_similarity<<<g, K5_THREADS, 0, s.stream>>>(s.lv[L - 1].d_lm, c->d_coff, c->d_tcoarse, c->d_active, CG.W, HW, CG.T, threshold,
+                                                     s.d_buf[0], s.d_counts + 0, s.cap, nullptr);
+    }
+    CK(cudaEventRecord(s.ev[1], s.stream));
+    CK(cudaEventSynchronize(s.ev[1]));
+    float ms = 0;
+    CK(cudaEventElapsedTime(&ms, s.ev[0], s.ev[1]));
+    *ms_per_launch = ms / iters;
     return 0;
 }
 }

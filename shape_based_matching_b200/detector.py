@@ -174,7 +174,57 @@ class Detector:
         """Candidates before sort/unique, in the reference's serial order (line2Dup.cpp:1124-1140)."""
         return self._run(self._L.sbm_match_candidates, source, threshold, class_ids, masks, cap)
 
+    def match_batch(self, frames, threshold, class_ids=(), masks=None, cap=None):
+        """Detector::match over a stream of equally shaped frames (sbm_match_batch): several frames are kept in
+        flight so that host->device copies overlap the kernels.  frames: sequence of HxW[xC] uint8 arrays (or one
+        [N,H,W,C] array; pinned memory keeps the copies asynchronous).  Returns a list of MATCH_REC arrays, one
+        per frame, each identical to match_records(frame)."""
+        imgs = [self._img(f) for f in frames]
+        n = len(imgs)
+        if n == 0:
+            return []
+        h, w, c = imgs[0].shape
+        for f in imgs:
+            if f.shape != (h, w, c):
+                raise ValueError("all frames of a batch must have the same shape")
+        ptrs = (C.c_void_p * n)(*[f.ctypes.data for f in imgs])
+        mptrs, keep = None, []
+        if masks is not None:
+            for m in masks:
+                if m is None:
+                    keep.append(None)
+                else:
+                    m = np.ascontiguousarray(m, dtype=np.uint8)
+                    if m.shape != (h, w):
+                        raise _capi.SbmError(-1, "mask.size() != source.size()")
+                    keep.append(m)
+            mptrs = (C.c_void_p * n)(*[(m.ctypes.data if m is not None else None) for m in keep])
+        arr, ncls, _keep = self._class_args(class_ids)
+        cap = cap or 256 * n
+        begin = (C.c_int * (n + 1))()
+        while True:
+            out = np.zeros(cap, MATCH_REC)
+            rc = self._L.sbm_match_batch(self._h, ptrs, mptrs, n, w, h, c, 0, C.c_float(threshold), arr, ncls,
+                                         out.ctypes.data_as(C.c_void_p), cap, begin)
+            if rc == -3 and begin[n] > cap:
+                cap = begin[n]
+                continue
+            check(rc)
+            return [out[begin[i] : begin[i + 1]].copy() for i in range(n)]
+
     # ---- device-resident path (bench `value`, multi-GPU) ----------------------------------------
+    def match_batch_device(self, d_imgs_ptr, frame_stride, n_frames, w, h, channels, threshold, class_ids, d_records, cap_per_frame,
+                           d_counts, stream=0):
+        arr, n, _keep = self._class_args(class_ids)
+        check(self._L.sbm_match_batch_device(self._h, C.c_void_p(d_imgs_ptr), frame_stride, n_frames, w, h, channels,
+                                             C.c_float(threshold), arr, n, C.c_void_p(d_records), cap_per_frame,
+                                             C.c_void_p(d_counts), C.c_void_p(stream) if stream else None))
+
+    def time_similarity(self, threshold, iters=20):
+        ms = C.c_float()
+        check(self._L.sbm_time_similarity(self._h, C.c_float(threshold), iters, C.byref(ms)))
+        return ms.value
+
     def match_device(self, d_img_ptr, w, h, channels, threshold, class_ids=(), d_records=0, cap=0, d_count=0, stream=0,
                      d_mask=0):
         arr, n, _keep = self._class_args(class_ids)
