@@ -163,6 +163,11 @@ int sbm_set_timing(sbm_ctx *ctx, int enable);
 /* Average device time of ONE k_similarity launch (the roofline kernel) on the most recent frame's linear memories:
  * `iters` back-to-back launches of the pipeline's own grid between two CUDA events on the launching stream. */
 int sbm_time_similarity(sbm_ctx *ctx, float threshold, int iters, float *ms_per_launch);
+/* Warm-cache device time per launch of every kernel of the pipeline on the most recent frame (same method):
+ * ms[3l+0] pyrDown of level l (0 for l = 0), ms[3l+1] orientation, ms[3l+2] spread+response+linearize,
+ * ms[3L] coarse similarity, ms[3L+1] refinement of the frame's coarse candidates at level L-2,
+ * ms[4L] one launch of the whole-frame CUDA graph (0 if none is instantiated).  n_ms >= 4L+1. */
+int sbm_time_kernels(sbm_ctx *ctx, float threshold, int iters, float *ms, int n_ms);
 
 #ifdef __cplusplus
 }

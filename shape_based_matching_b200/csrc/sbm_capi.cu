@@ -16,6 +16,7 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -49,6 +50,9 @@ int fail(int code, const char *fmt, ...)
     } while (0)
 
 constexpr int SBM_SLOTS = 4;
+#ifndef SBM_TALL_MIN
+#define SBM_TALL_MIN (2 * 148)
+#endif
 constexpr int COUNT_WORDS = 16; // [0..levels-1] stage counts, [10..11] u64 local evaluations
 constexpr uint32_t HEAD_RECS = 1024;
 
@@ -113,6 +117,18 @@ struct Slot
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     bool have_frame = false;
     int launches = 0;
+    // CUDA graph of the whole per-frame pipeline on this slot's buffers (see buildGraph)
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t gexec = nullptr;
+    uint64_t graph_epoch = 0;
+    float graph_threshold = 0.f;
+    bool graph_fetch = false;
+    const uint8_t *graph_src0 = nullptr;
+    // the two kernel nodes that read the level-0 frame, with what is needed to re-issue their parameters
+    cudaGraphNode_t n_orient0 = nullptr, n_pyr1 = nullptr;
+    void *f_orient0 = nullptr, *f_pyr1 = nullptr;
+    dim3 g_orient0, g_pyr1;
+    int graph_launches = 0;
 };
 } // namespace
 
@@ -134,6 +150,7 @@ struct sbm_ctx
     // frame shape
     int w = 0, h = 0, c = 0;
     uint64_t shape_gen = 0;
+    uint64_t epoch = 1; // bumped whenever anything a captured graph depends on changes
     std::vector<LevelGeom> geom;
     Slot slot[SBM_SLOTS];
 
@@ -217,6 +234,7 @@ int ensureShape(sbm_ctx *c, int w, int h, int ch)
     }
     c->w = w, c->h = h, c->c = ch;
     ++c->shape_gen;
+    ++c->epoch;
     c->coarse_dirty = true;
     return 0;
 }
@@ -251,6 +269,7 @@ int ensureSlot(sbm_ctx *c, Slot &s)
         }
         s.shape_gen = c->shape_gen;
         s.debug_bufs = c->debug;
+        s.graph_epoch = 0;
     }
     if (!s.d_buf[0])
     {
@@ -270,8 +289,18 @@ int ensureSlot(sbm_ctx *c, Slot &s)
     return 0;
 }
 
+void destroyGraph(Slot &s)
+{
+    if (s.gexec)
+        cudaGraphExecDestroy(s.gexec);
+    if (s.graph)
+        cudaGraphDestroy(s.graph);
+    s.gexec = nullptr, s.graph = nullptr, s.graph_epoch = 0;
+}
+
 void destroySlot(Slot &s)
 {
+    destroyGraph(s);
     freeSlotShape(s);
     freeDev(s.d_frame);
     freeDev(s.d_mask);
@@ -411,6 +440,7 @@ int ensureTemplates(sbm_ctx *c)
         if (!off.empty())
             CK(cudaMemcpy(c->d_coff, off.data(), off.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
         c->coarse_dirty = false;
+        ++c->epoch;
         c->active_dirty = true;
     }
     return 0;
@@ -454,6 +484,7 @@ int ensureActive(sbm_ctx *c, const int *class_idx, int n_classes)
         CK(cudaMemcpy(c->d_active, act.data(), act.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
     c->n_active = (uint32_t)act.size();
     c->active_dirty = false;
+    ++c->epoch;
     return 0;
 }
 
@@ -497,7 +528,7 @@ int enqueueFrame(sbm_ctx *c, Slot &s, const uint8_t *d_img, const uint8_t *d_mas
             ++launches;
         }
         // 64x32 tiles unless that leaves the GPU under two waves of CTAs; then 64x16
-        const bool tall = ((G.w + K1_TW - 1) / K1_TW) * ((G.h + 31) / 32) >= 2 * 148;
+        const bool tall = ((G.w + K1_TW - 1) / K1_TW) * ((G.h + 31) / 32) >= SBM_TALL_MIN;
         const int th = tall ? 32 : 16;
         dim3 g1((G.w + K1_TW - 1) / K1_TW, (G.h + th - 1) / th);
         if (c->c == 3 && tall)
@@ -569,6 +600,249 @@ int enqueueFrame(sbm_ctx *c, Slot &s, const uint8_t *d_img, const uint8_t *d_mas
     return 0;
 }
 
+// ------------------------------------------------------------------------------------------------
+// The per-frame pipeline as a CUDA graph.  All launches of a frame (1 memset + 3L+1+(L-1) kernels, and for the
+// host path the two D2H copies of the result head) become ONE cudaGraphLaunch: the CPU cost per frame drops from
+// ~12 driver calls to 2, and the two pyramid branches (orient/spread of level 0 vs pyrDown/orient/spread of
+// level 1) are independent nodes that the GPU may overlap.  The graph is rebuilt when anything baked into it
+// changes (frame shape, template set, active classes, threshold, buffer reallocation) -- tracked by ctx->epoch.
+// Only the level-0 source pointer is patched per launch (cudaGraphExecKernelNodeSetParams) when the caller's
+// frame lives somewhere else than last time.  Masks, debug taps and stage timing use the eager path.
+// ------------------------------------------------------------------------------------------------
+template <typename... A> int addKernel(cudaGraph_t g, cudaGraphNode_t *node, const std::vector<cudaGraphNode_t> &deps, void *func, dim3 grid,
+                                       dim3 block, A... args)
+{
+    void *argv[] = {(void *)&args...};
+    cudaKernelNodeParams p = {};
+    p.func = func;
+    p.gridDim = grid;
+    p.blockDim = block;
+    p.sharedMemBytes = 0;
+    p.kernelParams = argv;
+    p.extra = nullptr;
+    CK(cudaGraphAddKernelNode(node, g, deps.data(), deps.size(), &p));
+    return 0;
+}
+
+void *orientFunc(int ch, bool tall)
+{
+    if (ch == 3)
+        return tall ? (void *)k_orient<3, 32> : (void *)k_orient<3, 16>;
+    return tall ? (void *)k_orient<1, 32> : (void *)k_orient<1, 16>;
+}
+
+void *spreadFunc(int T)
+{
+    return T == 4 ? (void *)k_spread_linearize<4> : T == 8 ? (void *)k_spread_linearize<8> : T == 2 ? (void *)k_spread_linearize<2>
+                                                                                                     : (void *)k_spread_linearize<16>;
+}
+
+int buildGraph(sbm_ctx *c, Slot &s, const uint8_t *src0, float threshold, bool with_fetch)
+{
+    destroyGraph(s);
+    const int L = c->levels;
+    CK(cudaGraphCreate(&s.graph, 0));
+    cudaGraph_t g = s.graph;
+    int launches = 0;
+    s.n_orient0 = s.n_pyr1 = nullptr;
+
+    cudaGraphNode_t n_memset;
+    {
+        cudaMemsetParams mp = {};
+        mp.dst = s.d_counts;
+        mp.value = 0;
+        mp.elementSize = 4;
+        mp.width = COUNT_WORDS;
+        mp.height = 1;
+        mp.pitch = COUNT_WORDS * 4;
+        CK(cudaGraphAddMemsetNode(&n_memset, g, nullptr, 0, &mp));
+    }
+    const float weak_sq = c->weak * c->weak;
+    const uint8_t *null_mask = nullptr;
+    uint8_t *null_dbg = nullptr;
+    std::vector<cudaGraphNode_t> spread_node(L);
+    cudaGraphNode_t prev_src_node = nullptr; // producer of this level's source image
+    const uint8_t *src = src0;
+    int rc;
+    for (int l = 0; l < L; ++l)
+    {
+        const LevelGeom &G = c->geom[l];
+        LevelBuf &LB = s.lv[l];
+        std::vector<cudaGraphNode_t> dep_src;
+        if (l > 0)
+        {
+            const LevelGeom &P = c->geom[l - 1];
+            if (prev_src_node)
+                dep_src.push_back(prev_src_node);
+            cudaGraphNode_t n_pyr;
+            dim3 gp((G.w + 31) / 32, (G.h + 7) / 8);
+            void *f = c->c == 3 ? (void *)k_pyrdown<3> : (void *)k_pyrdown<1>;
+            if ((rc = addKernel(g, &n_pyr, dep_src, f, gp, dim3(256), src, P.w, P.h, LB.d_src, G.w, G.h)))
+                return rc;
+            if (l == 1)
+                s.n_pyr1 = n_pyr, s.f_pyr1 = f, s.g_pyr1 = gp;
+            src = LB.d_src;
+            prev_src_node = n_pyr;
+            dep_src.assign(1, n_pyr);
+            ++launches;
+        }
+        const bool tall = ((G.w + K1_TW - 1) / K1_TW) * ((G.h + 31) / 32) >= SBM_TALL_MIN;
+        const int th = tall ? 32 : 16;
+        dim3 g1((G.w + K1_TW - 1) / K1_TW, (G.h + th - 1) / th);
+        cudaGraphNode_t n_or, n_sp;
+        int mask_shift = l, mask_w = c->w;
+        if ((rc = addKernel(g, &n_or, dep_src, orientFunc(c->c, tall), g1, dim3(K1_THREADS), src, G.w, G.h, null_mask, mask_shift, mask_w, weak_sq,
+                            LB.d_quant)))
+            return rc;
+        if (l == 0)
+            s.n_orient0 = n_or, s.f_orient0 = orientFunc(c->c, tall), s.g_orient0 = g1;
+        dim3 g2((G.w + K2_PW - 1) / K2_PW, (G.h + K2_PH - 1) / K2_PH);
+        const uint8_t *qin = LB.d_quant;
+        if ((rc = addKernel(g, &n_sp, {n_or}, spreadFunc(G.T), g2, dim3(K2_THREADS), qin, G.w, G.h, LB.d_lm, null_dbg, null_dbg)))
+            return rc;
+        spread_node[l] = n_sp;
+        launches += 2;
+    }
+    // coarse similarity
+    const LevelGeom &CG = c->geom[L - 1];
+    const int HW = CG.W * CG.H;
+    cudaGraphNode_t tail = n_memset;
+    Cand *in = s.d_buf[0];
+    uint32_t in_cap = s.cap;
+    uint32_t *in_cnt = s.d_counts + 0;
+    if (c->n_active > 0)
+    {
+        dim3 gs(c->n_active, (HW + K5_TILE - 1) / K5_TILE);
+        const uint8_t *lm = s.lv[L - 1].d_lm;
+        const uint32_t *coff = c->d_coff, *act = c->d_active;
+        const TemplCoarse *tc = c->d_tcoarse;
+        uint16_t *nodump = nullptr;
+        cudaGraphNode_t n_sim;
+        if ((rc = addKernel(g, &n_sim, {n_memset, spread_node[L - 1]}, (void *)k_similarity, gs, dim3(K5_THREADS), lm, coff, tc, act, CG.W, HW, CG.T,
+                            threshold, in, in_cnt, in_cap, nodump)))
+            return rc;
+        tail = n_sim;
+        ++launches;
+    }
+    int stage = 1;
+    for (int l = L - 2; l >= 0; --l, ++stage)
+    {
+        const LevelGeom &G = c->geom[l];
+        Cand *out = s.d_buf[stage & 1];
+        uint32_t out_cap = s.cap;
+        uint32_t *out_cnt = s.d_counts + stage;
+        if (c->n_active > 0)
+        {
+            const uint8_t *lm = s.lv[l].d_lm;
+            const TemplLevel *tl = c->tl[l].d_tl;
+            const Feat *ff = c->tl[l].d_feats;
+            const Cand *cin = in;
+            const uint32_t *cin_cnt = in_cnt;
+            uint16_t *nodump = nullptr;
+            int raw_center = 0;
+            unsigned long long *ev = reinterpret_cast<unsigned long long *>(s.d_counts + 10);
+            cudaGraphNode_t n_ref;
+            if ((rc = addKernel(g, &n_ref, {tail, spread_node[l]}, (void *)k_refine, dim3(148 * 4), dim3(K6_THREADS), lm, tl, ff, cin, cin_cnt, in_cap,
+                                out, out_cnt, out_cap, G.w, G.h, G.T, threshold, nodump, raw_center, ev)))
+                return rc;
+            tail = n_ref;
+            ++launches;
+        }
+        in = out, in_cap = out_cap, in_cnt = out_cnt;
+    }
+    s.d_final = in;
+    s.d_final_count = in_cnt;
+    s.final_cap = in_cap;
+    if (with_fetch)
+    {
+        // tail depends on every other node transitively except possibly finer-level spreads when n_active == 0
+        std::vector<cudaGraphNode_t> deps{tail};
+        for (int l = 0; l < L; ++l)
+            deps.push_back(spread_node[l]);
+        cudaGraphNode_t n_c, n_r;
+        CK(cudaGraphAddMemcpyNode1D(&n_c, g, deps.data(), deps.size(), s.h_counts, s.d_counts, COUNT_WORDS * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+        const uint32_t head = std::min(HEAD_RECS, s.final_cap);
+        CK(cudaGraphAddMemcpyNode1D(&n_r, g, deps.data(), deps.size(), s.h_recs, s.d_final, (size_t)head * sizeof(Cand), cudaMemcpyDeviceToHost));
+    }
+    CK(cudaGraphInstantiate(&s.gexec, g, 0));
+    s.graph_epoch = c->epoch;
+    s.graph_threshold = threshold;
+    s.graph_fetch = with_fetch;
+    s.graph_src0 = src0;
+    s.graph_launches = launches;
+    return 0;
+}
+
+bool graphEligible(const sbm_ctx *c, const uint8_t *d_mask) { return !d_mask && !c->debug && !c->timing; }
+
+// one frame through the slot's graph on stream st (results in the slot's own buffers)
+int launchFrameGraph(sbm_ctx *c, Slot &s, const uint8_t *d_img, float threshold, bool with_fetch, cudaStream_t st)
+{
+    int rc;
+    if (!s.gexec || s.graph_epoch != c->epoch || s.graph_threshold != threshold || s.graph_fetch != with_fetch)
+    {
+        CK(cudaStreamSynchronize(s.stream));
+        if ((rc = buildGraph(c, s, d_img, threshold, with_fetch)))
+            return rc;
+    }
+    else if (s.graph_src0 != d_img)
+    {
+        // patch the two kernels that read the level-0 frame
+        const uint8_t *src = d_img, *null_mask = nullptr;
+        const float weak_sq = c->weak * c->weak;
+        {
+            const LevelGeom &G = c->geom[0];
+            int w = G.w, h = G.h, shift = 0, mask_w = c->w;
+            uint8_t *q = s.lv[0].d_quant;
+            void *argv[] = {&src, &w, &h, &null_mask, &shift, &mask_w, (void *)&weak_sq, &q};
+            cudaKernelNodeParams p = {};
+            p.func = s.f_orient0, p.gridDim = s.g_orient0, p.blockDim = dim3(K1_THREADS), p.kernelParams = argv;
+            CK(cudaGraphExecKernelNodeSetParams(s.gexec, s.n_orient0, &p));
+        }
+        if (s.n_pyr1)
+        {
+            const LevelGeom &P = c->geom[0], &G = c->geom[1];
+            int pw = P.w, ph = P.h, gw = G.w, gh = G.h;
+            uint8_t *dst = s.lv[1].d_src;
+            void *argv[] = {&src, &pw, &ph, &dst, &gw, &gh};
+            cudaKernelNodeParams p = {};
+            p.func = s.f_pyr1, p.gridDim = s.g_pyr1, p.blockDim = dim3(256), p.kernelParams = argv;
+            CK(cudaGraphExecKernelNodeSetParams(s.gexec, s.n_pyr1, &p));
+        }
+        s.graph_src0 = d_img;
+    }
+    CK(cudaGraphLaunch(s.gexec, st));
+    s.launches = s.graph_launches;
+    s.last_src0 = d_img;
+    s.have_frame = true;
+    return 0;
+}
+
+int enqueueFetch(Slot &s, cudaStream_t st);
+
+// one frame on slot s: through the graph when nothing frame-specific but the source pointer varies, else eagerly
+int runFrame(sbm_ctx *c, Slot &s, const uint8_t *d_img, const uint8_t *d_mask, float threshold, cudaStream_t st, bool with_fetch)
+{
+    int rc;
+    if (graphEligible(c, d_mask))
+        return launchFrameGraph(c, s, d_img, threshold, with_fetch, st);
+    if ((rc = enqueueFrame(c, s, d_img, d_mask, threshold, st, nullptr, 0, nullptr)))
+        return rc;
+    return with_fetch ? enqueueFetch(s, st) : 0;
+}
+
+int exportResults(Slot &s, cudaStream_t st, void *d_records, uint32_t cap, void *d_count)
+{
+    if (!d_records && !d_count)
+        return 0;
+    if (!d_records || !d_count)
+        return fail(SBM_ERR_BAD_ARG, "d_records and d_count must be given together");
+    k_export<<<8, 256, 0, st>>>(s.d_final, s.d_final_count, s.final_cap, (Cand *)d_records, cap, (uint32_t *)d_count);
+    ++s.launches;
+    CK(cudaGetLastError());
+    return 0;
+}
+
 int growCap(sbm_ctx *c, Slot &s, uint32_t need)
 {
     uint32_t nc = s.cap;
@@ -578,6 +852,7 @@ int growCap(sbm_ctx *c, Slot &s, uint32_t need)
     freeDev(s.d_buf[0]);
     freeDev(s.d_buf[1]);
     s.cap = nc;
+    s.graph_epoch = 0;
     return ensureSlot(c, s);
 }
 
@@ -717,7 +992,7 @@ int matchHost(sbm_ctx *c, const uint8_t *img, int w, int h, int ch, size_t strid
         return rc;
     for (int attempt = 0; attempt < 8; ++attempt)
     {
-        if ((rc = enqueueFrame(c, s, s.d_frame, dm, threshold, s.stream, nullptr, 0, nullptr)) || (rc = enqueueFetch(s, s.stream)))
+        if ((rc = runFrame(c, s, s.d_frame, dm, threshold, s.stream, true)))
             return rc;
         uint32_t n = 0;
         rc = finishFetch(c, s, s.stream, &n);
@@ -753,8 +1028,7 @@ int finishBatchFrame(sbm_ctx *c, Slot &s, const uint8_t *dm, float threshold, bo
             uint32_t need = 0;
             for (int k = 0; k < c->levels; ++k)
                 need = std::max(need, s.h_counts[k]);
-            if ((rc = growCap(c, s, need)) || (rc = enqueueFrame(c, s, s.d_frame, dm, threshold, s.stream, nullptr, 0, nullptr)) ||
-                (rc = enqueueFetch(s, s.stream)))
+            if ((rc = growCap(c, s, need)) || (rc = runFrame(c, s, s.d_frame, dm, threshold, s.stream, true)))
                 return rc;
             continue;
         }
@@ -923,8 +1197,7 @@ int sbm_match_batch(sbm_ctx *c, const uint8_t *const *imgs, const uint8_t *const
         if (i < n_frames)
         {
             if ((rc = uploadFrame(s, imgs[i], w, h, ch, stride, masks ? masks[i] : nullptr, &dm[i % SBM_SLOTS])) ||
-                (rc = enqueueFrame(c, s, s.d_frame, dm[i % SBM_SLOTS], threshold, s.stream, nullptr, 0, nullptr)) ||
-                (rc = enqueueFetch(s, s.stream)))
+                (rc = runFrame(c, s, s.d_frame, dm[i % SBM_SLOTS], threshold, s.stream, true)))
                 return rc;
         }
     }
@@ -946,8 +1219,12 @@ int sbm_match_device(sbm_ctx *c, const void *d_img, int w, int h, int ch, const 
         return rc;
     cudaStream_t st = stream ? (cudaStream_t)stream : s.stream;
     s.last_src0 = (const uint8_t *)d_img;
-    return enqueueFrame(c, s, (const uint8_t *)d_img, (const uint8_t *)d_mask, threshold, st, (Cand *)d_records,
-                        d_records ? (uint32_t)cap : 0, (uint32_t *)d_count);
+    if (!graphEligible(c, (const uint8_t *)d_mask))
+        return enqueueFrame(c, s, (const uint8_t *)d_img, (const uint8_t *)d_mask, threshold, st, (Cand *)d_records,
+                            d_records ? (uint32_t)cap : 0, (uint32_t *)d_count);
+    if ((rc = launchFrameGraph(c, s, (const uint8_t *)d_img, threshold, false, st)))
+        return rc;
+    return exportResults(s, st, d_records, (uint32_t)cap, d_count);
 }
 
 int sbm_match_batch_device(sbm_ctx *c, const void *d_imgs, size_t frame_stride, int n_frames, int w, int h, int ch, float threshold,
@@ -958,7 +1235,9 @@ int sbm_match_batch_device(sbm_ctx *c, const void *d_imgs, size_t frame_stride, 
     std::lock_guard<std::mutex> lock(c->mu);
     CK(cudaSetDevice(c->device));
     int rc;
-    const int ns = std::min(n_frames, SBM_SLOTS);
+    static const int env_slots = getenv("SBM_DEVICE_SLOTS") ? atoi(getenv("SBM_DEVICE_SLOTS")) : SBM_SLOTS;
+    const int NS = std::max(1, std::min(env_slots, SBM_SLOTS));
+    const int ns = std::min(n_frames, NS);
     for (int k = 0; k < ns; ++k)
         if ((rc = prepare(c, c->slot[k], w, h, ch, class_idx, n_classes)))
             return rc;
@@ -971,22 +1250,21 @@ int sbm_match_batch_device(sbm_ctx *c, const void *d_imgs, size_t frame_stride, 
         for (int k = 0; k < ns; ++k)
             CK(cudaStreamWaitEvent(c->slot[k].stream, s0.ev[0], 0));
     }
-    const bool timing = c->timing;
-    c->timing = false; // the per-stage events belong to the single-frame path
+    const bool timing = c->timing, debug = c->debug;
+    c->timing = false, c->debug = false; // stage events and debug taps belong to the single-frame path
     for (int i = 0; i < n_frames; ++i)
     {
-        Slot &s = c->slot[i % SBM_SLOTS];
+        Slot &s = c->slot[i % NS];
         const uint8_t *img = (const uint8_t *)d_imgs + (size_t)i * frame_stride;
-        s.last_src0 = img;
-        rc = enqueueFrame(c, s, img, nullptr, threshold, s.stream, (Cand *)d_records + (size_t)i * cap_per_frame, (uint32_t)cap_per_frame,
-                          (uint32_t *)d_counts + 2 * (size_t)i);
-        if (rc)
+        if ((rc = launchFrameGraph(c, s, img, threshold, false, s.stream)) ||
+            (rc = exportResults(s, s.stream, (Cand *)d_records + (size_t)i * cap_per_frame, (uint32_t)cap_per_frame,
+                                (uint32_t *)d_counts + 2 * (size_t)i)))
         {
-            c->timing = timing;
+            c->timing = timing, c->debug = debug;
             return rc;
         }
     }
-    c->timing = timing;
+    c->timing = timing, c->debug = debug;
     // join: the caller's stream continues after the last frame of every slot
     for (int k = 0; k < ns; ++k)
     {
@@ -1185,19 +1463,145 @@ int sbm_time_similarity(sbm_ctx *c, float threshold, int iters, float *ms_per_la
     const int HW = CG.W * CG.H;
     dim3 g(c->n_active, (HW + K5_TILE - 1) / K5_TILE);
     CK(cudaStreamSynchronize(s.stream));
-    for (int i = 0; i < iters + 3; ++i)
-    {
-        if (i == 3)
-            CK(cudaEventRecord(s.ev[0], s.stream));
+    // `iters` launches as one captured graph (stream launches are CPU-paced on this host, tools/launch_quant.cu)
+    cudaGraph_t tg = nullptr;
+    cudaGraphExec_t te = nullptr;
+    CK(cudaStreamBeginCapture(s.stream, cudaStreamCaptureModeThreadLocal));
+    for (int i = 0; i < iters; ++i)
         // same launch as the pipeline's; the candidate counter keeps running, records beyond cap are dropped
         k_similarity<<<g, K5_THREADS, 0, s.stream>>>(s.lv[L - 1].d_lm, c->d_coff, c->d_tcoarse, c->d_active, CG.W, HW, CG.T, threshold,
-                                                     s.d_buf[0], s.d_counts + 0, s.cap, nullptr);
-    }
+                                                     s.d_buf[1], s.d_counts + 12, 0u, nullptr);
+    CK(cudaStreamEndCapture(s.stream, &tg));
+    CK(cudaGraphInstantiate(&te, tg, 0));
+    CK(cudaGraphLaunch(te, s.stream));
+    CK(cudaEventRecord(s.ev[0], s.stream));
+    CK(cudaGraphLaunch(te, s.stream));
     CK(cudaEventRecord(s.ev[1], s.stream));
     CK(cudaEventSynchronize(s.ev[1]));
     float ms = 0;
     CK(cudaEventElapsedTime(&ms, s.ev[0], s.ev[1]));
+    cudaGraphExecDestroy(te);
+    cudaGraphDestroy(tg);
     *ms_per_launch = ms / iters;
+    return 0;
+}
+
+int sbm_time_kernels(sbm_ctx *c, float threshold, int iters, float *ms, int n_ms)
+{
+    if (!c || !ms || iters < 1)
+        return fail(SBM_ERR_BAD_ARG, "bad argument");
+    std::lock_guard<std::mutex> lock(c->mu);
+    Slot &s = c->slot[0];
+    if (!s.have_frame || c->n_active == 0 || !s.last_src0)
+        return fail(SBM_ERR_STATE, "no frame has been processed");
+    const int L = c->levels;
+    if (n_ms < 4 * L + 1)
+        return fail(SBM_ERR_BAD_ARG, "ms[] needs %d entries", 4 * L + 1);
+    CK(cudaSetDevice(c->device));
+    cudaStream_t st = s.stream;
+    CK(cudaStreamSynchronize(st));
+    const float weak_sq = c->weak * c->weak;
+    for (int i = 0; i < n_ms; ++i)
+        ms[i] = 0.f;
+    // run(k, body): `iters` back-to-back launches of one kernel between two events, after 2 warm-up launches
+#define SBM_TIME(slot_idx, launch)                                               \
+    do                                                                           \
+    {                                                                            \
+        /* `iters` launches captured into one graph: stream launches on this host are CPU-paced (~5 us each, */ \
+        /* 2 us quantum, tools/launch_quant.cu), graph nodes follow each other within ~0.7 us */               \
+        cudaGraph_t tg_ = nullptr;                                               \
+        cudaGraphExec_t te_ = nullptr;                                           \
+        CK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));        \
+        for (int it_ = 0; it_ < iters; ++it_)                                    \
+        {                                                                        \
+            launch;                                                              \
+        }                                                                        \
+        CK(cudaStreamEndCapture(st, &tg_));                                      \
+        CK(cudaGraphInstantiate(&te_, tg_, 0));                                  \
+        CK(cudaGraphLaunch(te_, st));                                            \
+        CK(cudaEventRecord(s.ev[0], st));                                        \
+        CK(cudaGraphLaunch(te_, st));                                            \
+        CK(cudaEventRecord(s.ev[1], st));                                        \
+        CK(cudaEventSynchronize(s.ev[1]));                                       \
+        float t_ = 0;                                                            \
+        CK(cudaEventElapsedTime(&t_, s.ev[0], s.ev[1]));                         \
+        ms[slot_idx] = t_ / iters;                                               \
+        cudaGraphExecDestroy(te_);                                               \
+        cudaGraphDestroy(tg_);                                                   \
+    } while (0)
+    const uint8_t *src = s.last_src0;
+    for (int l = 0; l < L; ++l)
+    {
+        const LevelGeom &G = c->geom[l];
+        LevelBuf &LB = s.lv[l];
+        if (l > 0)
+        {
+            const LevelGeom &P = c->geom[l - 1];
+            dim3 g((G.w + 31) / 32, (G.h + 7) / 8);
+            if (c->c == 3)
+                SBM_TIME(3 * l + 0, (k_pyrdown<3><<<g, 256, 0, st>>>(src, P.w, P.h, LB.d_src, G.w, G.h)));
+            else
+                SBM_TIME(3 * l + 0, (k_pyrdown<1><<<g, 256, 0, st>>>(src, P.w, P.h, LB.d_src, G.w, G.h)));
+            src = LB.d_src;
+        }
+        const bool tall = ((G.w + K1_TW - 1) / K1_TW) * ((G.h + 31) / 32) >= SBM_TALL_MIN;
+        const int th = tall ? 32 : 16;
+        dim3 g1((G.w + K1_TW - 1) / K1_TW, (G.h + th - 1) / th);
+        const uint8_t *nm = nullptr;
+        if (c->c == 3 && tall)
+            SBM_TIME(3 * l + 1, (k_orient<3, 32><<<g1, K1_THREADS, 0, st>>>(src, G.w, G.h, nm, l, c->w, weak_sq, LB.d_quant)));
+        else if (c->c == 3)
+            SBM_TIME(3 * l + 1, (k_orient<3, 16><<<g1, K1_THREADS, 0, st>>>(src, G.w, G.h, nm, l, c->w, weak_sq, LB.d_quant)));
+        else if (tall)
+            SBM_TIME(3 * l + 1, (k_orient<1, 32><<<g1, K1_THREADS, 0, st>>>(src, G.w, G.h, nm, l, c->w, weak_sq, LB.d_quant)));
+        else
+            SBM_TIME(3 * l + 1, (k_orient<1, 16><<<g1, K1_THREADS, 0, st>>>(src, G.w, G.h, nm, l, c->w, weak_sq, LB.d_quant)));
+        dim3 g2((G.w + K2_PW - 1) / K2_PW, (G.h + K2_PH - 1) / K2_PH);
+        uint8_t *nd = nullptr;
+        if (G.T == 4)
+            SBM_TIME(3 * l + 2, (k_spread_linearize<4><<<g2, K2_THREADS, 0, st>>>(LB.d_quant, G.w, G.h, LB.d_lm, nd, nd)));
+        else if (G.T == 8)
+            SBM_TIME(3 * l + 2, (k_spread_linearize<8><<<g2, K2_THREADS, 0, st>>>(LB.d_quant, G.w, G.h, LB.d_lm, nd, nd)));
+        else if (G.T == 2)
+            SBM_TIME(3 * l + 2, (k_spread_linearize<2><<<g2, K2_THREADS, 0, st>>>(LB.d_quant, G.w, G.h, LB.d_lm, nd, nd)));
+        else
+            SBM_TIME(3 * l + 2, (k_spread_linearize<16><<<g2, K2_THREADS, 0, st>>>(LB.d_quant, G.w, G.h, LB.d_lm, nd, nd)));
+    }
+    const LevelGeom &CG = c->geom[L - 1];
+    const int HW = CG.W * CG.H;
+    dim3 gs(c->n_active, (HW + K5_TILE - 1) / K5_TILE);
+    // scratch counters so that the frame's real candidate counts stay intact
+    uint32_t *d_tmp = nullptr;
+    CK(cudaMalloc(&d_tmp, COUNT_WORDS * 4));
+    CK(cudaMemsetAsync(d_tmp, 0, COUNT_WORDS * 4, st));
+    SBM_TIME(3 * L, (k_similarity<<<gs, K5_THREADS, 0, st>>>(s.lv[L - 1].d_lm, c->d_coff, c->d_tcoarse, c->d_active, CG.W, HW, CG.T, threshold,
+                                                             s.d_buf[1], d_tmp, 0u, nullptr)));
+    // refinement of the frame's own coarse candidates (stage counts of the last real run), output discarded
+    int stage = 1;
+    for (int l = L - 2; l >= 0; --l, ++stage)
+    {
+        const LevelGeom &G = c->geom[l];
+        if (stage == 1)
+            SBM_TIME(3 * L + stage, (k_refine<<<148 * 4, K6_THREADS, 0, st>>>(s.lv[l].d_lm, c->tl[l].d_tl, c->tl[l].d_feats, s.d_buf[0], s.d_counts + 0,
+                                                                              s.cap, s.d_buf[1], d_tmp + 1, 0u, G.w, G.h, G.T, threshold, nullptr, 0,
+                                                                              reinterpret_cast<unsigned long long *>(d_tmp + 10))));
+    }
+    if (s.gexec && s.graph_epoch == c->epoch)
+    {
+        CK(cudaGraphLaunch(s.gexec, st));
+        CK(cudaEventRecord(s.ev[0], st));
+        for (int it = 0; it < iters; ++it)
+            CK(cudaGraphLaunch(s.gexec, st));
+        CK(cudaEventRecord(s.ev[1], st));
+        CK(cudaEventSynchronize(s.ev[1]));
+        float t = 0;
+        CK(cudaEventElapsedTime(&t, s.ev[0], s.ev[1]));
+        ms[4 * L] = t / iters;
+    }
+#undef SBM_TIME
+    CK(cudaStreamSynchronize(st));
+    cudaFree(d_tmp);
+    CK(cudaGetLastError());
     return 0;
 }
 }

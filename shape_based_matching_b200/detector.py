@@ -220,6 +220,22 @@ class Detector:
                                              C.c_float(threshold), arr, n, C.c_void_p(d_records), cap_per_frame,
                                              C.c_void_p(d_counts), C.c_void_p(stream) if stream else None))
 
+    def time_kernels(self, threshold, iters=20):
+        L = self.pyramid_levels
+        ms = np.zeros(4 * L + 1, np.float32)
+        check(self._L.sbm_time_kernels(self._h, C.c_float(threshold), iters, ms.ctypes.data_as(C.c_void_p), ms.size))
+        out = {}
+        for l in range(L):
+            if l:
+                out["pyrdown_L%d" % l] = float(ms[3 * l])
+            out["orient_L%d" % l] = float(ms[3 * l + 1])
+            out["spread_linearize_L%d" % l] = float(ms[3 * l + 2])
+        out["similarity"] = float(ms[3 * L])
+        if L > 1:
+            out["refine_L%d" % (L - 2)] = float(ms[3 * L + 1])
+        out["frame_graph"] = float(ms[4 * L])
+        return out
+
     def time_similarity(self, threshold, iters=20):
         ms = C.c_float()
         check(self._L.sbm_time_similarity(self._h, C.c_float(threshold), iters, C.byref(ms)))
