@@ -20,6 +20,7 @@
  *                                                                                    line2Dup.cpp:1106-1117
  *   sbm_similarity_map      similarity / similarity_64                                line2Dup.cpp:807-858,924-984
  *   sbm_similarity_local    similarityLocal / similarityLocal_64                      line2Dup.cpp:860-922,986-1048
+ *   sbm_quantized_orientations  quantizedOrientations + hysteresisGradient + pyrDown (training)  line2Dup.cpp:218-444
  */
 #ifndef SBM_CAPI_H
 #define SBM_CAPI_H
@@ -149,6 +150,15 @@ int sbm_get_intermediate(sbm_ctx *ctx, int level, int kind, void *dst, size_t by
 int sbm_similarity_map(sbm_ctx *ctx, int class_idx, int template_id, uint16_t *dst, size_t bytes);
 /* Raw u16 [16][16] local sums at pyramid level `level` around centre (x,y) (level coordinates). */
 int sbm_similarity_local(sbm_ctx *ctx, int class_idx, int template_id, int level, int x, int y, uint16_t *dst);
+
+/* Training front end (Detector::addTemplate -> ColorGradientPyramid::update, line2Dup.cpp:406-444): the image is taken
+ * `level` times through cv::pyrDown (size cols/2 x rows/2 each time) and then through quantizedOrientations +
+ * hysteresisGradient (:218-404) on the GPU.  Any image size is accepted (no T constraints: templates are cropped
+ * objects).  Outputs (each may be NULL), all [h_out][w_out] of the reached level: magnitude = dx*dx+dy*dy of the
+ * strongest channel (float), angle_ori = phase in degrees (float), angle = one-hot quantised label (u8, 0 = none);
+ * src_level = the pyrDown'ed source itself, u8 [h_out][w_out][channels]. */
+int sbm_quantized_orientations(sbm_ctx *ctx, const uint8_t *img, int w, int h, int channels, size_t stride, int level,
+                               float *magnitude, float *angle_ori, uint8_t *angle, uint8_t *src_level, int *w_out, int *h_out);
 
 /* Counters of the most recent frame: [0] coarse evaluations (sum over matched templates of
  * in-image features * template_positions), [1] coarse candidates, [2] local evaluations,

@@ -17,7 +17,7 @@ SYMBOLS = [
     "sbm_last_error", "sbm_build_info", "sbm_create", "sbm_destroy", "sbm_set_class_templates", "sbm_clear_templates",
     "sbm_num_templates", "sbm_match", "sbm_match_candidates", "sbm_match_device", "sbm_device_results",
     "sbm_finalize_records", "sbm_set_debug", "sbm_get_intermediate", "sbm_similarity_map", "sbm_similarity_local",
-    "sbm_last_stats", "sbm_last_timing", "sbm_set_timing", "sbm_match_batch", "sbm_match_batch_device", "sbm_time_similarity", "sbm_time_kernels",
+    "sbm_last_stats", "sbm_last_timing", "sbm_set_timing", "sbm_match_batch", "sbm_match_batch_device", "sbm_time_similarity", "sbm_time_kernels", "sbm_quantized_orientations",
 ]
 
 SBM_QUANTIZED, SBM_SPREAD, SBM_RESPONSE, SBM_LINEAR, SBM_PYRAMID_SRC = range(5)
@@ -56,6 +56,7 @@ def lib():
         L.sbm_match_batch_device.argtypes = [vp, vp, C.c_size_t, ci, ci, ci, ci, cf, vp, ci, vp, ci, vp, vp]
         L.sbm_time_similarity.argtypes = [vp, cf, ci, C.POINTER(cf)]
         L.sbm_time_kernels.argtypes = [vp, cf, ci, vp, ci]
+        L.sbm_quantized_orientations.argtypes = [vp, vp, ci, ci, ci, C.c_size_t, ci, vp, vp, vp, vp, C.POINTER(ci), C.POINTER(ci)]
         L.sbm_device_results.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(ci)]
         L.sbm_finalize_records.argtypes = [vp, vp, ci, vp, ci, ci, vp, ci, C.POINTER(ci)]
         L.sbm_set_debug.argtypes = [vp, ci]

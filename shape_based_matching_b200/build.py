@@ -47,6 +47,26 @@ def build_cuda(force=False):
     return LIB
 
 
+HOST_LIB = os.path.join(PKG, "libline2Dup_b200.so")
+DRIVER = os.path.join(ROOT, "tests", "cpp", "dropin_driver")
+
+
+def build_host(force=False):
+    """The drop-in C++ API (include/line2Dup.h) over the C ABI, and the C++ test driver that uses it."""
+    inc = os.path.join(ROOT, "include")
+    src = os.path.join(PKG, "csrc", "line2Dup.cpp")
+    deps = [src, os.path.join(inc, "line2Dup.h"), os.path.join(inc, "sbm_capi.h"), os.path.join(inc, "sbm", "cv_compat.hpp"),
+            os.path.join(inc, "sbm", "imgproc_compat.hpp"), LIB]
+    if force or _stale(HOST_LIB, deps):
+        _run([HOST_CXX, "-std=c++17", "-O2", "-fPIC", "-shared", "-Wall", "-I" + inc, src, "-o", HOST_LIB, "-L" + PKG, "-lsbm_b200", "-lz",
+              "-Wl,-rpath,$ORIGIN"])
+    drv = os.path.join(ROOT, "tests", "cpp", "dropin_driver.cpp")
+    if os.path.exists(drv) and (force or _stale(DRIVER, [drv, HOST_LIB])):
+        _run([HOST_CXX, "-std=c++17", "-O2", "-Wall", "-I" + inc, drv, "-o", DRIVER, "-L" + PKG, "-lline2Dup_b200", "-lsbm_b200", "-lz",
+              "-Wl,-rpath,$ORIGIN/../../shape_based_matching_b200"])
+    return HOST_LIB
+
+
 def build_oracle(force=False):
     """Build the CHECKER (test infrastructure): the C restatement and, where the reference tree exists,
     the reference's own code (oracle/_ref).  Building it is not using it."""
@@ -65,6 +85,7 @@ def build_oracle(force=False):
 
 def build_all(force=False):
     build_cuda(force)
+    build_host(force)
     build_oracle(force)
 
 

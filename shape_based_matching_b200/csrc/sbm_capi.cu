@@ -532,13 +532,13 @@ int enqueueFrame(sbm_ctx *c, Slot &s, const uint8_t *d_img, const uint8_t *d_mas
         const int th = tall ? 32 : 16;
         dim3 g1((G.w + K1_TW - 1) / K1_TW, (G.h + th - 1) / th);
         if (c->c == 3 && tall)
-            k_orient<3, 32><<<g1, K1_THREADS, 0, st>>>(src, G.w, G.h, d_mask, l, c->w, weak_sq, LB.d_quant);
+            k_orient<3, 32><<<g1, K1_THREADS, 0, st>>>(src, G.w, G.h, d_mask, l, c->w, weak_sq, LB.d_quant, nullptr, nullptr);
         else if (c->c == 3)
-            k_orient<3, 16><<<g1, K1_THREADS, 0, st>>>(src, G.w, G.h, d_mask, l, c->w, weak_sq, LB.d_quant);
+            k_orient<3, 16><<<g1, K1_THREADS, 0, st>>>(src, G.w, G.h, d_mask, l, c->w, weak_sq, LB.d_quant, nullptr, nullptr);
         else if (tall)
-            k_orient<1, 32><<<g1, K1_THREADS, 0, st>>>(src, G.w, G.h, d_mask, l, c->w, weak_sq, LB.d_quant);
+            k_orient<1, 32><<<g1, K1_THREADS, 0, st>>>(src, G.w, G.h, d_mask, l, c->w, weak_sq, LB.d_quant, nullptr, nullptr);
         else
-            k_orient<1, 16><<<g1, K1_THREADS, 0, st>>>(src, G.w, G.h, d_mask, l, c->w, weak_sq, LB.d_quant);
+            k_orient<1, 16><<<g1, K1_THREADS, 0, st>>>(src, G.w, G.h, d_mask, l, c->w, weak_sq, LB.d_quant, nullptr, nullptr);
         dim3 g2((G.w + K2_PW - 1) / K2_PW, (G.h + K2_PH - 1) / K2_PH);
         uint8_t *ds = c->debug ? LB.d_spread : nullptr, *dr = c->debug ? LB.d_resp : nullptr;
         if (G.T == 4)
@@ -660,6 +660,7 @@ int buildGraph(sbm_ctx *c, Slot &s, const uint8_t *src0, float threshold, bool w
     const float weak_sq = c->weak * c->weak;
     const uint8_t *null_mask = nullptr;
     uint8_t *null_dbg = nullptr;
+    float *null_f = nullptr;
     std::vector<cudaGraphNode_t> spread_node(L);
     cudaGraphNode_t prev_src_node = nullptr; // producer of this level's source image
     const uint8_t *src = src0;
@@ -692,7 +693,7 @@ int buildGraph(sbm_ctx *c, Slot &s, const uint8_t *src0, float threshold, bool w
         cudaGraphNode_t n_or, n_sp;
         int mask_shift = l, mask_w = c->w;
         if ((rc = addKernel(g, &n_or, dep_src, orientFunc(c->c, tall), g1, dim3(K1_THREADS), src, G.w, G.h, null_mask, mask_shift, mask_w, weak_sq,
-                            LB.d_quant)))
+                            LB.d_quant, null_f, null_f)))
             return rc;
         if (l == 0)
             s.n_orient0 = n_or, s.f_orient0 = orientFunc(c->c, tall), s.g_orient0 = g1;
@@ -794,7 +795,8 @@ int launchFrameGraph(sbm_ctx *c, Slot &s, const uint8_t *d_img, float threshold,
             const LevelGeom &G = c->geom[0];
             int w = G.w, h = G.h, shift = 0, mask_w = c->w;
             uint8_t *q = s.lv[0].d_quant;
-            void *argv[] = {&src, &w, &h, &null_mask, &shift, &mask_w, (void *)&weak_sq, &q};
+            float *null_f = nullptr;
+            void *argv[] = {&src, &w, &h, &null_mask, &shift, &mask_w, (void *)&weak_sq, &q, &null_f, &null_f};
             cudaKernelNodeParams p = {};
             p.func = s.f_orient0, p.gridDim = s.g_orient0, p.blockDim = dim3(K1_THREADS), p.kernelParams = argv;
             CK(cudaGraphExecKernelNodeSetParams(s.gexec, s.n_orient0, &p));
@@ -1549,13 +1551,13 @@ int sbm_time_kernels(sbm_ctx *c, float threshold, int iters, float *ms, int n_ms
         dim3 g1((G.w + K1_TW - 1) / K1_TW, (G.h + th - 1) / th);
         const uint8_t *nm = nullptr;
         if (c->c == 3 && tall)
-            SBM_TIME(3 * l + 1, (k_orient<3, 32><<<g1, K1_THREADS, 0, st>>>(src, G.w, G.h, nm, l, c->w, weak_sq, LB.d_quant)));
+            SBM_TIME(3 * l + 1, (k_orient<3, 32><<<g1, K1_THREADS, 0, st>>>(src, G.w, G.h, nm, l, c->w, weak_sq, LB.d_quant, nullptr, nullptr)));
         else if (c->c == 3)
-            SBM_TIME(3 * l + 1, (k_orient<3, 16><<<g1, K1_THREADS, 0, st>>>(src, G.w, G.h, nm, l, c->w, weak_sq, LB.d_quant)));
+            SBM_TIME(3 * l + 1, (k_orient<3, 16><<<g1, K1_THREADS, 0, st>>>(src, G.w, G.h, nm, l, c->w, weak_sq, LB.d_quant, nullptr, nullptr)));
         else if (tall)
-            SBM_TIME(3 * l + 1, (k_orient<1, 32><<<g1, K1_THREADS, 0, st>>>(src, G.w, G.h, nm, l, c->w, weak_sq, LB.d_quant)));
+            SBM_TIME(3 * l + 1, (k_orient<1, 32><<<g1, K1_THREADS, 0, st>>>(src, G.w, G.h, nm, l, c->w, weak_sq, LB.d_quant, nullptr, nullptr)));
         else
-            SBM_TIME(3 * l + 1, (k_orient<1, 16><<<g1, K1_THREADS, 0, st>>>(src, G.w, G.h, nm, l, c->w, weak_sq, LB.d_quant)));
+            SBM_TIME(3 * l + 1, (k_orient<1, 16><<<g1, K1_THREADS, 0, st>>>(src, G.w, G.h, nm, l, c->w, weak_sq, LB.d_quant, nullptr, nullptr)));
         dim3 g2((G.w + K2_PW - 1) / K2_PW, (G.h + K2_PH - 1) / K2_PH);
         uint8_t *nd = nullptr;
         if (G.T == 4)
@@ -1602,6 +1604,72 @@ int sbm_time_kernels(sbm_ctx *c, float threshold, int iters, float *ms, int n_ms
     CK(cudaStreamSynchronize(st));
     cudaFree(d_tmp);
     CK(cudaGetLastError());
+    return 0;
+}
+
+int sbm_quantized_orientations(sbm_ctx *c, const uint8_t *img, int w, int h, int ch, size_t stride, int level, float *magnitude,
+                               float *angle_ori, uint8_t *angle, uint8_t *src_level, int *w_out, int *h_out)
+{
+    if (!c || !img || level < 0 || level > 8)
+        return fail(SBM_ERR_BAD_ARG, "bad argument");
+    if (ch != 1 && ch != 3)
+        return fail(SBM_ERR_BAD_ARG, "source must have 1 or 3 channels (got %d)", ch);
+    if ((w >> level) < 1 || (h >> level) < 1)
+        return fail(SBM_ERR_BAD_ARG, "image too small for pyramid level %d", level);
+    std::lock_guard<std::mutex> lock(c->mu);
+    CK(cudaSetDevice(c->device));
+    Slot &s = c->slot[0];
+    if (!s.stream)
+        CK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+    cudaStream_t st = s.stream;
+    const size_t row = (size_t)w * ch;
+    uint8_t *d_a = nullptr, *d_b = nullptr, *d_q = nullptr;
+    float *d_mag = nullptr, *d_ang = nullptr;
+    CK(cudaMalloc(&d_a, row * h));
+    if (stride == 0 || stride == row)
+        CK(cudaMemcpyAsync(d_a, img, row * h, cudaMemcpyHostToDevice, st));
+    else
+        CK(cudaMemcpy2DAsync(d_a, row, img, stride, row, h, cudaMemcpyHostToDevice, st));
+    int lw = w, lh = h;
+    for (int l = 1; l <= level; ++l) // cv::pyrDown(src, src, Size(cols/2, rows/2))  line2Dup.cpp:431-433
+    {
+        const int dw = lw / 2, dh = lh / 2;
+        CK(cudaMalloc(&d_b, (size_t)dw * dh * ch));
+        dim3 g((dw + 31) / 32, (dh + 7) / 8);
+        if (ch == 3)
+            k_pyrdown<3><<<g, 256, 0, st>>>(d_a, lw, lh, d_b, dw, dh);
+        else
+            k_pyrdown<1><<<g, 256, 0, st>>>(d_a, lw, lh, d_b, dw, dh);
+        CK(cudaStreamSynchronize(st));
+        cudaFree(d_a);
+        d_a = d_b, d_b = nullptr;
+        lw = dw, lh = dh;
+    }
+    const size_t px = (size_t)lw * lh;
+    CK(cudaMalloc(&d_q, px));
+    CK(cudaMalloc(&d_mag, px * sizeof(float)));
+    CK(cudaMalloc(&d_ang, px * sizeof(float)));
+    dim3 g1((lw + K1_TW - 1) / K1_TW, (lh + 15) / 16);
+    const float weak_sq = c->weak * c->weak;
+    if (ch == 3)
+        k_orient<3, 16><<<g1, K1_THREADS, 0, st>>>(d_a, lw, lh, nullptr, 0, lw, weak_sq, d_q, d_mag, d_ang);
+    else
+        k_orient<1, 16><<<g1, K1_THREADS, 0, st>>>(d_a, lw, lh, nullptr, 0, lw, weak_sq, d_q, d_mag, d_ang);
+    CK(cudaGetLastError());
+    if (magnitude)
+        CK(cudaMemcpyAsync(magnitude, d_mag, px * sizeof(float), cudaMemcpyDeviceToHost, st));
+    if (angle_ori)
+        CK(cudaMemcpyAsync(angle_ori, d_ang, px * sizeof(float), cudaMemcpyDeviceToHost, st));
+    if (angle)
+        CK(cudaMemcpyAsync(angle, d_q, px, cudaMemcpyDeviceToHost, st));
+    if (src_level)
+        CK(cudaMemcpyAsync(src_level, d_a, px * ch, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    cudaFree(d_a), cudaFree(d_q), cudaFree(d_mag), cudaFree(d_ang);
+    if (w_out)
+        *w_out = lw;
+    if (h_out)
+        *h_out = lh;
     return 0;
 }
 }

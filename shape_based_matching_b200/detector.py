@@ -220,6 +220,24 @@ class Detector:
                                              C.c_float(threshold), arr, n, C.c_void_p(d_records), cap_per_frame,
                                              C.c_void_p(d_counts), C.c_void_p(stream) if stream else None))
 
+    def quantized_orientations(self, source, level=0):
+        """ColorGradientPyramid::update at pyramid level `level` (line2Dup.cpp:406-444) on the GPU
+        -> (magnitude f32, angle_ori f32 degrees, angle u8 one-hot), each [h >> level][w >> level]."""
+        img = self._img(source)
+        h, w, c = img.shape
+        lw, lh = w, h
+        for _ in range(level):
+            lw, lh = lw // 2, lh // 2
+        mag = np.zeros((lh, lw), np.float32)
+        ang = np.zeros((lh, lw), np.float32)
+        q = np.zeros((lh, lw), np.uint8)
+        wo, ho = C.c_int(), C.c_int()
+        check(self._L.sbm_quantized_orientations(self._h, img.ctypes.data_as(C.c_void_p), w, h, c, 0, level,
+                                                 mag.ctypes.data_as(C.c_void_p), ang.ctypes.data_as(C.c_void_p),
+                                                 q.ctypes.data_as(C.c_void_p), None, C.byref(wo), C.byref(ho)))
+        assert (wo.value, ho.value) == (lw, lh)
+        return mag, ang, q
+
     def time_kernels(self, threshold, iters=20):
         L = self.pyramid_levels
         ms = np.zeros(4 * L + 1, np.float32)

@@ -44,3 +44,41 @@ def to_gray(img):
     import cv2
 
     return cv2.cvtColor(img, cv2.COLOR_BGR2GRAY)
+
+
+def write_templates_yaml(path, class_id, tdesc, feats):
+    """A class in the OpenCV FileStorage YAML 1.0 dialect the reference writes (line2Dup.cpp:86-113, :1548-1575;
+    sample: /root/reference/test/case1/test_templ.yaml:1-20)."""
+    n, levels = tdesc.shape[:2]
+    out = ["%YAML:1.0", "---", "class_id: %s" % class_id, "pyramid_levels: %d" % levels, "template_pyramids:"]
+    fo = 0
+    for t in range(n):
+        out += ["   -", "      template_id: %d" % t, "      templates:"]
+        for l in range(levels):
+            wd, ht, tx, ty, nf = (int(v) for v in tdesc[t, l])
+            out += ["         -", "            width: %d" % wd, "            height: %d" % ht, "            tl_x: %d" % tx,
+                    "            tl_y: %d" % ty, "            pyramid_level: %d" % l, "            features:"]
+            for x, y, lab in feats[fo : fo + nf]:
+                out.append("               - [ %d, %d, %d ]" % (x, y, lab))
+            fo += nf
+    with open(path, "w") as f:
+        f.write("\n".join(out) + "\n")
+
+
+def parse_driver_templates(text):
+    """'T t L l w h tlx tly nf n : x,y,label ...' lines of tests/cpp/dropin_driver -> (tdesc[n, levels, 5], feats[sum, 3])"""
+    import numpy as np
+
+    rows, feats = {}, []
+    for line in text.splitlines():
+        if not line.startswith("T "):
+            continue
+        head, _, tail = line.partition(":")
+        h = head.split()
+        t, l = int(h[1]), int(h[3])
+        rows[(t, l)] = [int(h[4]), int(h[5]), int(h[6]), int(h[7]), int(h[9])]
+        feats += [[int(v) for v in tok.split(",")] for tok in tail.split()]
+    n = 1 + max(k[0] for k in rows)
+    levels = 1 + max(k[1] for k in rows)
+    tdesc = np.array([[rows[(t, l)] for l in range(levels)] for t in range(n)], np.int32)
+    return tdesc, np.array(feats, np.int32).reshape(-1, 3)
