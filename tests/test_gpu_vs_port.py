@@ -1,0 +1,102 @@
+"""GPU parity on seeded synthetic inputs against the C++ restatement (oracle/sbm_oracle.cpp, itself pinned to the
+reference's goldens by tests/test_oracle_port.py): shapes, channel counts, T sets, pyramid depths and masks the
+fixtures do not cover.  Bar: byte-exact intermediates, identical candidate and final lists."""
+import numpy as np
+import pytest
+
+from oracle import port
+
+pytestmark = pytest.mark.gpu
+
+
+def synth_image(rng, h, w, c):
+    import cv2
+
+    img = cv2.GaussianBlur(rng.integers(0, 256, (h, w, c), dtype=np.uint8), (5, 5), 0).reshape(h, w, c) // 3
+    for _ in range(6):  # bright polygons and ellipses: strong, coherent edges
+        col = [int(v) for v in rng.integers(120, 256, c)]
+        if rng.random() < 0.5:
+            pts = rng.integers(0, [w, h], (4, 2)).astype(np.int32)
+            cv2.fillPoly(img, [pts], col)
+        else:
+            cv2.ellipse(img, (int(rng.integers(0, w)), int(rng.integers(0, h))), (int(rng.integers(8, w // 3)), int(rng.integers(8, h // 3))),
+                        float(rng.integers(0, 180)), 0, 360, col, -1)
+    return np.ascontiguousarray(img)
+
+
+def synth_templates(rng, n, levels, box, nf0):
+    """n template pyramids: random features inside a box that halves per level (like cropTemplates' output)"""
+    tdesc = np.zeros((n, levels, 5), np.int32)
+    feats = []
+    for t in range(n):
+        for l in range(levels):
+            bw, bh = max(box[0] >> l, 4), max(box[1] >> l, 4)
+            nf = max(nf0 >> l, 3)
+            tdesc[t, l] = (bw, bh, 0, 0, nf)
+            f = np.stack([rng.integers(0, bw + 1, nf), rng.integers(0, bh + 1, nf), rng.integers(0, 8, nf)], 1)
+            feats.append(f)
+    return tdesc, np.concatenate(feats).astype(np.int32)
+
+
+CONFIGS = [
+    # h, w, c, T, n_templates, box, nf, threshold, use_mask
+    (128, 160, 3, (4, 8), 12, (40, 36), 24, 35.0, False),
+    (128, 160, 1, (4, 8), 12, (40, 36), 24, 35.0, True),
+    (96, 96, 1, (4,), 6, (30, 30), 70, 30.0, False),       # single level, > 63 features (u16 accumulation path)
+    (256, 192, 3, (4, 4, 8), 8, (64, 48), 40, 30.0, False),  # three pyramid levels
+    (192, 320, 3, (8, 8), 5, (100, 60), 200, 30.0, False),   # wide template, many features
+    (64, 64, 3, (2, 4), 4, (16, 16), 12, 30.0, False),       # T = 2 at level 0 (rows not a multiple of 4 bytes * 3)
+]
+
+
+@pytest.mark.parametrize("cfg", CONFIGS, ids=[str(i) for i in range(len(CONFIGS))])
+def test_cuda_equals_port(cfg):
+    from shape_based_matching_b200 import Detector
+
+    h, w, c, T, n, box, nf, thr, use_mask = cfg
+    rng = np.random.default_rng(hash(cfg) & 0xFFFF)
+    img = synth_image(rng, h, w, c)
+    mask = None
+    if use_mask:
+        mask = np.full((h, w), 255, np.uint8)
+        mask[: h // 3, : w // 2] = 0
+    tdesc, feats = synth_templates(rng, n, len(T), box, nf)
+    det = Detector(nf, T, 30.0, 60.0)
+    det.setClassTemplates("c", tdesc, feats)
+    det.set_debug(True)
+    orc = port.PortDetector(T, 30.0)
+    orc.add_class(tdesc, feats)
+    orc.process(img, mask)
+    got = det.match_records(img, thr, ["c"], masks=mask)
+    for l in range(len(T)):
+        for kind in range(4):
+            a, b = det.intermediate(l, kind), orc.get(l, kind)
+            bad = np.flatnonzero(a != b)
+            assert bad.size == 0, "level %d kind %d: %d bytes differ, first at %s" % (l, kind, bad.size, bad[:5])
+    hw = ((h >> (len(T) - 1)) // T[-1], (w >> (len(T) - 1)) // T[-1])
+    for t in range(n):
+        assert np.array_equal(det.similarity_map("c", t, hw), orc.similarity(0, t)), "raw similarity map of template %d" % t
+    cand, want_cand = det.match_candidates(img, thr, ["c"], masks=mask), orc.match(thr, finalize=False)
+    assert len(want_cand) > 0, "config produces no candidates: not a test"
+    for name, a, b in (("candidates", cand, want_cand), ("final", got, orc.match(thr, finalize=True))):
+        assert len(a) == len(b), "%s: %d vs %d" % (name, len(a), len(b))
+        for k in ("x", "y", "template_id"):
+            assert np.array_equal(a[k], b[k]), (name, k)
+        assert np.array_equal(a["similarity"].view(np.uint32), b["similarity"].view(np.uint32)), name
+
+
+def test_local_patch_sums():
+    from shape_based_matching_b200 import Detector
+
+    rng = np.random.default_rng(5)
+    img = synth_image(rng, 256, 256, 3)
+    tdesc, feats = synth_templates(rng, 3, 2, (60, 60), 90)
+    det = Detector(90, (4, 8))
+    det.setClassTemplates("c", tdesc, feats)
+    det.match_records(img, 50.0, ["c"])
+    orc = port.PortDetector((4, 8), 30.0)
+    orc.add_class(tdesc, feats)
+    orc.process(img)
+    for t in range(3):
+        for (x, y) in ((32, 32), (100, 77), (163, 131)):
+            assert np.array_equal(det.similarity_local("c", t, 0, x, y), orc.similarity_local(0, t, 0, x, y))
