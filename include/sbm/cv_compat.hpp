@@ -327,6 +327,22 @@ public:
         Mat out(rows, cols, CV_MAKETYPE(ddepth, cn));
         const bool ident = (alpha == 1.0 && beta == 0.0);
         const float a = (float)alpha, b = (float)beta;
+        if (depth() == CV_32F && ddepth == CV_8U && beta == 0.0)
+        {
+            // the conversion on the match() path (line2Dup.cpp:225): a plain loop the compiler vectorises;
+            // same arithmetic as the generic path below (float multiply, round half to even, saturate)
+            const float *s = ptr<float>(0);
+            uchar *d = out.ptr(0);
+            const size_t n = (size_t)rows * cols * cn;
+            for (size_t i = 0; i < n; ++i)
+            {
+                const float v = ident ? s[i] : s[i] * a;
+                const float cl = v < 0.f ? 0.f : (v > 255.f ? 255.f : v); // NaN falls through to lrintf like before
+                d[i] = (uchar)lrintf(cl);
+            }
+            dst = out;
+            return;
+        }
         for (int r = 0; r < rows; ++r)
             for (int c = 0; c < cols * cn; ++c)
             {
