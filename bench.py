@@ -302,6 +302,42 @@ def main():
     ms_per_step = ms / args.steps
     value = evals_step / (ms_per_step * 1e-3)
 
+    # ---- N > 1: the other way the path shards: every rank matches the SAME frames against its slice
+    # of the 360 templates (interleaved ids), one all_gather of the record lists per step (strong scaling) ----
+    tshard = None
+    if world > 1:
+        from shape_based_matching_b200.sharding import ShardedDetector
+
+        sdet = ShardedDetector(nf, (4, 8), 30.0, 60.0, device=local_rank, rec_cap=REC_CAP)
+        sdet.setClassTemplates(cid, tdesc, feats)
+        got = sdet.match(gold["img"], THRESHOLD, [cid])  # parity guard through the real NCCL all_gather
+        if len(got) != len(gold["matches"]) or not np.array_equal(got["template_id"], gold["matches"]["template_id"]) or not np.array_equal(
+                got["similarity"].view(np.uint32), gold["matches"]["similarity"].view(np.uint32)):
+            raise SystemExit("bench.py: template-sharded list disagrees with the golden reference list")
+        s_frames = torch.from_numpy(make_frames(base, B, 1000)).to(dev)  # the same frames on every rank
+
+        def step_tshard():
+            sdet.det.match_batch_device(s_frames.data_ptr(), frame_bytes, B, W, H, C, THRESHOLD, [cid], d_recs.data_ptr(), REC_CAP,
+                                        d_cnt.data_ptr(), sptr)
+            dist.all_gather_into_tensor(g_cnt, d_cnt)
+            dist.all_gather_into_tensor(g_recs, d_recs)
+
+        for _ in range(args.warmup):
+            step_tshard()
+        barrier()
+        e0.record(stream)
+        for _ in range(args.steps):
+            step_tshard()
+        e1.record(stream)
+        barrier()
+        tms = torch.tensor([e0.elapsed_time(e1) / args.steps], dtype=torch.float64, device=dev)
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+        tshard = {"sharding": "templates (rank r holds ids r, r+N, ...; every rank builds the frame's linear memories)",
+                  "scaling": "strong", "templates_per_gpu": int(sdet.det.numTemplates()), "frames_per_step": B,
+                  "ms_per_frame": float(tms[0]) / B, "evals_per_s": (evals_step_rank / (float(tms[0]) * 1e-3)),
+                  "parity": "merged list identical to the golden reference list"}
+        sdet.det.close()
+
     # ---- single-stream latency per frame (frames strictly one after the other) ----
     for _ in range(2):
         step_device_serial()
@@ -423,6 +459,8 @@ def main():
         "gpu_launches": launches_per_frame * B * args.steps,
         "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline,
     }
+    if tshard:
+        line["template_sharded"] = tshard
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

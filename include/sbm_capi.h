@@ -20,6 +20,7 @@
  *                                                                                    line2Dup.cpp:1106-1117
  *   sbm_similarity_map      similarity / similarity_64                                line2Dup.cpp:807-858,924-984
  *   sbm_similarity_local    similarityLocal / similarityLocal_64                      line2Dup.cpp:860-922,986-1048
+ *   sbm_merge_shard_records the `matches.insert(...)` reduction over templates + sort/unique, across GPUs   line2Dup.cpp:1124-1145,1166-1170
  *   sbm_quantized_orientations  quantizedOrientations + hysteresisGradient + pyrDown (training)  line2Dup.cpp:218-444
  */
 #ifndef SBM_CAPI_H
@@ -139,6 +140,20 @@ int sbm_device_results(sbm_ctx *ctx, void **d_records, void **d_count, int *cap)
  * list: same ordering + std::sort + std::unique as sbm_match.  finalize != 0 applies sort/unique. */
 int sbm_finalize_records(sbm_ctx *ctx, const sbm_device_rec *recs, int n, const int *class_idx, int n_classes,
                          int finalize, sbm_match_rec *out, int cap, int *n_out);
+
+/* Template sharding over several GPUs (templates are independent given the frame's linear memories,
+ * line2Dup.cpp:1166-1170): every rank installs a slice of each class and matches the same frame; the ranks'
+ * sbm_device_rec lists are exchanged (NCCL allgather) and merged here.  No context and no GPU needed: pure host code.
+ *   recs         the ranks' records laid end to end, rank 0 first; n_per_rank[n_ranks] how many each rank produced
+ *   class_sizes  int[n_ranks][n_classes]: templates of class slot k installed on rank r (template_gid of a
+ *                record is LOCAL to its rank: class slot 0's templates first, then slot 1, ...)
+ *   mode         SBM_SHARD_INTERLEAVED: rank r holds global ids r, r+G, r+2G, ... of every class;
+ *                SBM_SHARD_CONTIGUOUS : rank r holds the block that follows the blocks of ranks < r
+ * Output as sbm_finalize_records: the reference's serial candidate order over GLOBAL template ids, then
+ * (finalize != 0) Detector::match's std::sort + std::unique (line2Dup.cpp:1143-1145). */
+enum { SBM_SHARD_INTERLEAVED = 0, SBM_SHARD_CONTIGUOUS = 1 };
+int sbm_merge_shard_records(const sbm_device_rec *recs, const int *n_per_rank, int n_ranks, const int *class_sizes, int n_classes,
+                            int mode, int finalize, sbm_match_rec *out, int cap, int *n_out);
 
 /* Copy an intermediate of the most recent frame to host memory `dst` (`bytes` must match exactly;
  * pass dst == NULL to query the size through *bytes_needed).  SPREAD and RESPONSE are only materialised

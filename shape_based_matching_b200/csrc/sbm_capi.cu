@@ -1303,6 +1303,86 @@ int sbm_finalize_records(sbm_ctx *c, const sbm_device_rec *recs, int n, const in
     return orderRecords(c, reinterpret_cast<const Cand *>(recs), (uint32_t)n, finalize != 0, out, cap, n_out);
 }
 
+// Template-sharded matching: the merge step after the allgather.  Pure host code, no context: the
+// reference's candidate order is (class order, template_id ascending, coarse scan order) (line2Dup.cpp:1124-1140,
+// :1170, :1200-1216), so the ranks' records are re-labelled with GLOBAL template ids, ordered that way and fed
+// to the same std::sort + std::unique as Detector::match (:1143-1145).
+int sbm_merge_shard_records(const sbm_device_rec *recs, const int *n_per_rank, int n_ranks, const int *class_sizes, int n_classes,
+                            int mode, int finalize, sbm_match_rec *out, int cap, int *n_out)
+{
+    if (!n_per_rank || !class_sizes || !n_out || n_ranks < 1 || n_classes < 1 || (mode != SBM_SHARD_INTERLEAVED && mode != SBM_SHARD_CONTIGUOUS))
+        return fail(SBM_ERR_BAD_ARG, "sbm_merge_shard_records: bad arguments");
+    struct G
+    {
+        int32_t cls, tid;
+        uint32_t key;
+        const sbm_device_rec *r;
+    };
+    std::vector<G> g;
+    size_t at = 0;
+    for (int rk = 0; rk < n_ranks; ++rk)
+    {
+        const int *cs = class_sizes + (size_t)rk * n_classes;
+        std::vector<uint32_t> begin(n_classes + 1, 0);
+        for (int k = 0; k < n_classes; ++k)
+        {
+            if (cs[k] < 0)
+                return fail(SBM_ERR_BAD_ARG, "negative class size");
+            begin[k + 1] = begin[k] + (uint32_t)cs[k];
+        }
+        if (n_per_rank[rk] < 0 || (n_per_rank[rk] > 0 && !recs))
+            return fail(SBM_ERR_BAD_ARG, "bad record count of rank %d", rk);
+        for (int i = 0; i < n_per_rank[rk]; ++i, ++at)
+        {
+            const sbm_device_rec &r = recs[at];
+            if (r.template_gid >= begin[n_classes])
+                return fail(SBM_ERR_BAD_ARG, "rank %d record %d names local template %u of %u", rk, i, r.template_gid, begin[n_classes]);
+            const int k = (int)(std::upper_bound(begin.begin(), begin.end(), r.template_gid) - begin.begin()) - 1;
+            const int local = (int)(r.template_gid - begin[k]);
+            int tid;
+            if (mode == SBM_SHARD_INTERLEAVED)
+                tid = rk + local * n_ranks; // rank rk owns ids rk, rk + G, rk + 2G, ...
+            else
+            {
+                tid = local; // rank rk owns a contiguous block after the blocks of the lower ranks
+                for (int q = 0; q < rk; ++q)
+                    tid += class_sizes[(size_t)q * n_classes + k];
+            }
+            g.push_back(G{k, tid, r.order_key, &r});
+        }
+    }
+    std::sort(g.begin(), g.end(), [](const G &a, const G &b) {
+        if (a.cls != b.cls)
+            return a.cls < b.cls;
+        if (a.tid != b.tid)
+            return a.tid < b.tid;
+        return a.key < b.key;
+    });
+    std::vector<sbm_match_rec> m;
+    m.reserve(g.size());
+    for (const G &e : g)
+        m.push_back(sbm_match_rec{e.r->x, e.r->y, e.r->similarity, e.cls, e.tid});
+    if (finalize)
+    {
+        std::sort(m.begin(), m.end(), [](const sbm_match_rec &a, const sbm_match_rec &b) {
+            if (a.similarity != b.similarity)
+                return a.similarity > b.similarity;
+            return a.template_id < b.template_id;
+        });
+        m.erase(std::unique(m.begin(), m.end(),
+                            [](const sbm_match_rec &a, const sbm_match_rec &b) {
+                                return a.x == b.x && a.y == b.y && a.similarity == b.similarity && a.class_idx == b.class_idx;
+                            }),
+                m.end());
+    }
+    *n_out = (int)m.size();
+    if ((int)m.size() > cap)
+        return fail(SBM_ERR_CAPACITY, "output holds %d matches, %zu needed", cap, m.size());
+    if (!m.empty() && out)
+        memcpy(out, m.data(), m.size() * sizeof(sbm_match_rec));
+    return 0;
+}
+
 int sbm_set_debug(sbm_ctx *c, int enable)
 {
     if (!c)
