@@ -519,11 +519,11 @@ int enqueueFrame(sbm_ctx *c, Slot &s, const uint8_t *d_img, const uint8_t *d_mas
         if (l > 0)
         {
             const LevelGeom &P = c->geom[l - 1];
-            dim3 g((G.w + 31) / 32, (G.h + 7) / 8);
+            dim3 g((G.w + 31) / 32, (G.h + K1B_ROWS - 1) / K1B_ROWS);
             if (c->c == 3)
-                k_pyrdown<3><<<g, 256, 0, st>>>(src, P.w, P.h, LB.d_src, G.w, G.h);
+                k_pyrdown<3><<<g, K1B_THREADS, 0, st>>>(src, P.w, P.h, LB.d_src, G.w, G.h);
             else
-                k_pyrdown<1><<<g, 256, 0, st>>>(src, P.w, P.h, LB.d_src, G.w, G.h);
+                k_pyrdown<1><<<g, K1B_THREADS, 0, st>>>(src, P.w, P.h, LB.d_src, G.w, G.h);
             src = LB.d_src;
             ++launches;
         }
@@ -676,9 +676,9 @@ int buildGraph(sbm_ctx *c, Slot &s, const uint8_t *src0, float threshold, bool w
             if (prev_src_node)
                 dep_src.push_back(prev_src_node);
             cudaGraphNode_t n_pyr;
-            dim3 gp((G.w + 31) / 32, (G.h + 7) / 8);
+            dim3 gp((G.w + 31) / 32, (G.h + K1B_ROWS - 1) / K1B_ROWS);
             void *f = c->c == 3 ? (void *)k_pyrdown<3> : (void *)k_pyrdown<1>;
-            if ((rc = addKernel(g, &n_pyr, dep_src, f, gp, dim3(256), src, P.w, P.h, LB.d_src, G.w, G.h)))
+            if ((rc = addKernel(g, &n_pyr, dep_src, f, gp, dim3(K1B_THREADS), src, P.w, P.h, LB.d_src, G.w, G.h)))
                 return rc;
             if (l == 1)
                 s.n_pyr1 = n_pyr, s.f_pyr1 = f, s.g_pyr1 = gp;
@@ -808,7 +808,7 @@ int launchFrameGraph(sbm_ctx *c, Slot &s, const uint8_t *d_img, float threshold,
             uint8_t *dst = s.lv[1].d_src;
             void *argv[] = {&src, &pw, &ph, &dst, &gw, &gh};
             cudaKernelNodeParams p = {};
-            p.func = s.f_pyr1, p.gridDim = s.g_pyr1, p.blockDim = dim3(256), p.kernelParams = argv;
+            p.func = s.f_pyr1, p.gridDim = s.g_pyr1, p.blockDim = dim3(K1B_THREADS), p.kernelParams = argv;
             CK(cudaGraphExecKernelNodeSetParams(s.gexec, s.n_pyr1, &p));
         }
         s.graph_src0 = d_img;
@@ -1619,11 +1619,11 @@ int sbm_time_kernels(sbm_ctx *c, float threshold, int iters, float *ms, int n_ms
         if (l > 0)
         {
             const LevelGeom &P = c->geom[l - 1];
-            dim3 g((G.w + 31) / 32, (G.h + 7) / 8);
+            dim3 g((G.w + 31) / 32, (G.h + K1B_ROWS - 1) / K1B_ROWS);
             if (c->c == 3)
-                SBM_TIME(3 * l + 0, (k_pyrdown<3><<<g, 256, 0, st>>>(src, P.w, P.h, LB.d_src, G.w, G.h)));
+                SBM_TIME(3 * l + 0, (k_pyrdown<3><<<g, K1B_THREADS, 0, st>>>(src, P.w, P.h, LB.d_src, G.w, G.h)));
             else
-                SBM_TIME(3 * l + 0, (k_pyrdown<1><<<g, 256, 0, st>>>(src, P.w, P.h, LB.d_src, G.w, G.h)));
+                SBM_TIME(3 * l + 0, (k_pyrdown<1><<<g, K1B_THREADS, 0, st>>>(src, P.w, P.h, LB.d_src, G.w, G.h)));
             src = LB.d_src;
         }
         const bool tall = ((G.w + K1_TW - 1) / K1_TW) * ((G.h + 31) / 32) >= SBM_TALL_MIN;
@@ -1715,11 +1715,11 @@ int sbm_quantized_orientations(sbm_ctx *c, const uint8_t *img, int w, int h, int
     {
         const int dw = lw / 2, dh = lh / 2;
         CK(cudaMalloc(&d_b, (size_t)dw * dh * ch));
-        dim3 g((dw + 31) / 32, (dh + 7) / 8);
+        dim3 g((dw + 31) / 32, (dh + K1B_ROWS - 1) / K1B_ROWS);
         if (ch == 3)
-            k_pyrdown<3><<<g, 256, 0, st>>>(d_a, lw, lh, d_b, dw, dh);
+            k_pyrdown<3><<<g, K1B_THREADS, 0, st>>>(d_a, lw, lh, d_b, dw, dh);
         else
-            k_pyrdown<1><<<g, 256, 0, st>>>(d_a, lw, lh, d_b, dw, dh);
+            k_pyrdown<1><<<g, K1B_THREADS, 0, st>>>(d_a, lw, lh, d_b, dw, dh);
         CK(cudaStreamSynchronize(st));
         cudaFree(d_a);
         d_a = d_b, d_b = nullptr;
@@ -1732,9 +1732,9 @@ int sbm_quantized_orientations(sbm_ctx *c, const uint8_t *img, int w, int h, int
     dim3 g1((lw + K1_TW - 1) / K1_TW, (lh + 15) / 16);
     const float weak_sq = c->weak * c->weak;
     if (ch == 3)
-        k_orient<3, 16><<<g1, K1_THREADS, 0, st>>>(d_a, lw, lh, nullptr, 0, lw, weak_sq, d_q, d_mag, d_ang);
+        k_orient<3, 16, true><<<g1, K1_THREADS, 0, st>>>(d_a, lw, lh, nullptr, 0, lw, weak_sq, d_q, d_mag, d_ang);
     else
-        k_orient<1, 16><<<g1, K1_THREADS, 0, st>>>(d_a, lw, lh, nullptr, 0, lw, weak_sq, d_q, d_mag, d_ang);
+        k_orient<1, 16, true><<<g1, K1_THREADS, 0, st>>>(d_a, lw, lh, nullptr, 0, lw, weak_sq, d_q, d_mag, d_ang);
     CK(cudaGetLastError());
     if (magnitude)
         CK(cudaMemcpyAsync(magnitude, d_mag, px * sizeof(float), cudaMemcpyDeviceToHost, st));
