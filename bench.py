@@ -363,6 +363,8 @@ def main():
     # the roofline kernel alone: back-to-back launches of the pipeline's own k_similarity grid between two events
     sim_ms = det.time_similarity(THRESHOLD, iters=50)
     kernel_ms = det.time_kernels(THRESHOLD, iters=20)
+    lm_bytes = 8 * (W // 2) * (H // 2)  # the coarse level's linear memories: 8 labels x (512 x 512) bytes
+    l2_gbs = det.time_l2_read(lm_bytes, iters=20)
 
     # ---- end to end through the public API: pinned host frame -> final host list, every frame ----
     pinned = torch.from_numpy(frames).pin_memory()
@@ -411,6 +413,9 @@ def main():
         "traffic_source": "profiles/r1c_summary.md (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum, one launch)",
         "peak_source": peak_src,
         "algorithmic_bytes_per_launch": coarse, "avg_launch_ms": sim_ms,
+        "l2": {"read_peak_gbs": l2_gbs, "frac": sim_gbs / l2_gbs, "working_set_bytes": lm_bytes,
+               "how": "sbm_time_l2_read: every CTA of a 592-CTA grid streams a buffer of the working-set size with ld.global.cg.v4 "
+                      "(L1 bypassed), CUDA events; k_similarity's gather is served by L1 + L2, so this is a reference point, not a hard bound"},
         "how": "50 launches of the pipeline's own k_similarity grid, captured as one CUDA graph, between two CUDA events on the "
                "launching stream (sbm_time_similarity); stream launches on this host are CPU-paced at ~5 us (tools/launch_quant.cu)",
         "kernel_ms_warm": kernel_ms,

@@ -188,6 +188,10 @@ int sbm_set_timing(sbm_ctx *ctx, int enable);
 /* Average device time of ONE k_similarity launch (the roofline kernel) on the most recent frame's linear memories:
  * `iters` back-to-back launches of the pipeline's own grid between two CUDA events on the launching stream. */
 int sbm_time_similarity(sbm_ctx *ctx, float threshold, int iters, float *ms_per_launch);
+/* Read bandwidth of an L2-resident buffer of `bytes` bytes (GB/s; 16-byte loads that bypass L1, all SMs, CUDA events):
+ * the second denominator SURVEY 8d asks for next to the HBM copy peak, since the coarse linear memories (2 MiB at
+ * M1) never leave L2.  A measurement aid, not part of the match path. */
+int sbm_time_l2_read(sbm_ctx *ctx, size_t bytes, int iters, float *gb_per_s);
 /* Warm-cache device time per launch of every kernel of the pipeline on the most recent frame (same method):
  * ms[3l+0] pyrDown of level l (0 for l = 0), ms[3l+1] orientation, ms[3l+2] spread+response+linearize,
  * ms[3L] coarse similarity, ms[3L+1] refinement of the frame's coarse candidates at level L-2,

@@ -17,7 +17,7 @@ SYMBOLS = [
     "sbm_last_error", "sbm_build_info", "sbm_create", "sbm_destroy", "sbm_set_class_templates", "sbm_clear_templates",
     "sbm_num_templates", "sbm_match", "sbm_match_candidates", "sbm_match_device", "sbm_device_results",
     "sbm_finalize_records", "sbm_set_debug", "sbm_get_intermediate", "sbm_similarity_map", "sbm_similarity_local",
-    "sbm_last_stats", "sbm_last_timing", "sbm_set_timing", "sbm_match_batch", "sbm_match_batch_device", "sbm_time_similarity", "sbm_time_kernels", "sbm_quantized_orientations", "sbm_merge_shard_records",
+    "sbm_last_stats", "sbm_last_timing", "sbm_set_timing", "sbm_match_batch", "sbm_match_batch_device", "sbm_time_similarity", "sbm_time_kernels", "sbm_quantized_orientations", "sbm_merge_shard_records", "sbm_time_l2_read",
 ]
 
 SBM_QUANTIZED, SBM_SPREAD, SBM_RESPONSE, SBM_LINEAR, SBM_PYRAMID_SRC = range(5)
@@ -59,6 +59,7 @@ def lib():
         L.sbm_quantized_orientations.argtypes = [vp, vp, ci, ci, ci, C.c_size_t, ci, vp, vp, vp, vp, C.POINTER(ci), C.POINTER(ci)]
         L.sbm_device_results.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(ci)]
         L.sbm_finalize_records.argtypes = [vp, vp, ci, vp, ci, ci, vp, ci, C.POINTER(ci)]
+        L.sbm_time_l2_read.argtypes = [vp, C.c_size_t, ci, C.POINTER(cf)]
         L.sbm_merge_shard_records.argtypes = [vp, vp, ci, vp, ci, ci, ci, vp, ci, C.POINTER(ci)]
         L.sbm_set_debug.argtypes = [vp, ci]
         L.sbm_set_timing.argtypes = [vp, ci]

@@ -926,9 +926,10 @@ int finishFetch(sbm_ctx *c, Slot &s, cudaStream_t st, uint32_t *n_out)
         {
             cudaFreeHost(s.h_recs);
             s.h_recs = nullptr;
-            s.h_recs_cap = n;
-            CK(cudaMallocHost(&s.h_recs, (size_t)n * sizeof(Cand)));
+            s.h_recs_cap = std::max(n, 2 * s.h_recs_cap);
+            CK(cudaMallocHost(&s.h_recs, (size_t)s.h_recs_cap * sizeof(Cand)));
             head = 0;
+            s.graph_epoch = 0; // the slot's graph holds the old host pointer in its fetch node: rebuild before the next launch
         }
         CK(cudaMemcpyAsync(s.h_recs + head, s.d_final + head, (size_t)(n - head) * sizeof(Cand), cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));
@@ -1565,6 +1566,39 @@ int sbm_time_similarity(sbm_ctx *c, float threshold, int iters, float *ms_per_la
     cudaGraphExecDestroy(te);
     cudaGraphDestroy(tg);
     *ms_per_launch = ms / iters;
+    return 0;
+}
+
+int sbm_time_l2_read(sbm_ctx *c, size_t bytes, int iters, float *gb_per_s)
+{
+    if (!c || !gb_per_s || iters < 1 || bytes < 4096 || bytes > ((size_t)1 << 30))
+        return fail(SBM_ERR_BAD_ARG, "bad argument");
+    std::lock_guard<std::mutex> lock(c->mu);
+    CK(cudaSetDevice(c->device));
+    Slot &s = c->slot[0];
+    const uint32_t n_vec = (uint32_t)(bytes / 16 / 1024 * 1024); // whole 1024-vector rounds only
+    if (n_vec == 0)
+        return fail(SBM_ERR_BAD_ARG, "buffer too small");
+    void *d = nullptr;
+    uint32_t *sink = nullptr;
+    CK(cudaMalloc(&d, (size_t)n_vec * 16));
+    CK(cudaMalloc(&sink, 4));
+    CK(cudaMemsetAsync(d, 1, (size_t)n_vec * 16, s.stream));
+    int sms = 0;
+    CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device));
+    const int grid = sms * 4, reps = 8;
+    k_l2_read<<<grid, 256, 0, s.stream>>>((const uint4 *)d, n_vec, reps, sink); // warm-up: pulls the buffer into L2
+    CK(cudaEventRecord(s.ev[0], s.stream));
+    for (int i = 0; i < iters; ++i)
+        k_l2_read<<<grid, 256, 0, s.stream>>>((const uint4 *)d, n_vec, reps, sink);
+    CK(cudaEventRecord(s.ev[1], s.stream));
+    CK(cudaEventSynchronize(s.ev[1]));
+    CK(cudaGetLastError());
+    float ms = 0;
+    CK(cudaEventElapsedTime(&ms, s.ev[0], s.ev[1]));
+    cudaFree(d);
+    cudaFree(sink);
+    *gb_per_s = (float)((double)n_vec * 16.0 * reps * grid * iters / (ms * 1e-3) / 1e9);
     return 0;
 }
 

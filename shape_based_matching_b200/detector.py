@@ -259,6 +259,12 @@ class Detector:
         check(self._L.sbm_time_similarity(self._h, C.c_float(threshold), iters, C.byref(ms)))
         return ms.value
 
+    def time_l2_read(self, nbytes=2 << 20, iters=20):
+        """GB/s of 16-byte L1-bypassing loads over an L2-resident buffer (roofline denominator for k_similarity)"""
+        g = C.c_float()
+        check(self._L.sbm_time_l2_read(self._h, nbytes, iters, C.byref(g)))
+        return g.value
+
     def match_device(self, d_img_ptr, w, h, channels, threshold, class_ids=(), d_records=0, cap=0, d_count=0, stream=0,
                      d_mask=0):
         arr, n, _keep = self._class_args(class_ids)

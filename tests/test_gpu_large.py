@@ -1,0 +1,196 @@
+"""BASELINE.json configs 4 and 5 at full size on the GPU (C4 = 4096^2 frame x 3600 templates with
+8191 / 4095 features, C5 = 2048^2 frames x 720 templates with 128 / 64 features).
+
+C5 is small enough for the CPU restatement (oracle/sbm_oracle.cpp, pinned to the reference's goldens): full lists
+are compared.  C4 costs ~9e11 byte-adds per frame, hours on the oracle, so parity there is shown through
+(a) an oracle check of a template subset, against both a subset-only run and the full run filtered to the subset,
+(b) known answers: every template is cut from the frame's own quantised orientations, so it must be found at its
+    origin with similarity exactly 100 (raw sum 4 * 8191 = 32764, the largest value the u16 accumulators ever hold),
+(c) linearity: the raw similarity map of a template equals the sum of the maps of its two halves,
+(d) sharding invariance: 8 template shards merged == the unsharded list."""
+import numpy as np
+import pytest
+
+from oracle import port
+
+pytestmark = pytest.mark.gpu
+
+
+def dense_image(rng, h, w, c, n_shapes):
+    import cv2
+
+    img = np.full((h, w, c), 40, np.uint8)
+    for _ in range(n_shapes):
+        col = [int(v) for v in rng.integers(0, 256, c)]
+        cx, cy = int(rng.integers(0, w)), int(rng.integers(0, h))
+        if rng.random() < 0.5:
+            pts = (np.array([cx, cy]) + rng.integers(-90, 91, (5, 2))).astype(np.int32)
+            cv2.fillPoly(img, [pts], col)
+        else:
+            cv2.ellipse(img, (cx, cy), (int(rng.integers(10, 90)), int(rng.integers(10, 90))), float(rng.integers(0, 180)), 0, 360, col, -1)
+    return np.ascontiguousarray(img.reshape(h, w, c))
+
+
+def cut_templates(rng, quant, n, win, nf, origins):
+    """n template pyramids cut from the frame's own quantised images quant[l] ([h_l][w_l], one-hot): template t sits at
+    origins[t % len(origins)] (level-0 pixels, multiples of 16) and takes nf[l] random labelled pixels of its window."""
+    levels = len(quant)
+    tdesc = np.zeros((n, levels, 5), np.int32)
+    feats = []
+    cache = {}
+    for t in range(n):
+        ox, oy = origins[t % len(origins)]
+        for l in range(levels):
+            key = (ox, oy, l)
+            if key not in cache:
+                x0, y0, wl = ox >> l, oy >> l, win >> l
+                sub = quant[l][y0 : y0 + wl, x0 : x0 + wl]
+                ys, xs = np.nonzero(sub)
+                lab = np.log2(sub[ys, xs].astype(np.float64)).astype(np.int32)
+                cache[key] = np.stack([xs.astype(np.int32), ys.astype(np.int32), lab], 1)
+            pool = cache[key]
+            assert pool.shape[0] >= nf[l], "window at %s level %d has only %d labelled pixels" % ((ox, oy), l, pool.shape[0])
+            pick = rng.choice(pool.shape[0], nf[l], replace=False)
+            feats.append(pool[pick])
+            tdesc[t, l] = (win >> l, win >> l, 0, 0, nf[l])
+    return tdesc, np.ascontiguousarray(np.concatenate(feats).astype(np.int32))
+
+
+def quantised_pyramid(orc, shape, levels):
+    return [orc.get(l, 0).reshape(shape[0] >> l, shape[1] >> l) for l in range(levels)]
+
+
+def assert_found_at_origin(cands, n, origins):
+    """every template, cut from this very frame, is matched at its origin with similarity exactly 100 (the reported
+    position is the cell's x*T + T/2 - 1, line2Dup.cpp:1211-1212, :1284-1285: origin + 1 for T = 4)"""
+    best = {}
+    for r in cands:  # serial candidate order: the first entry of a template is not necessarily its best
+        t = int(r["template_id"])
+        if t not in best or r["similarity"] > best[t]["similarity"]:
+            best[t] = r
+    for t in range(n):
+        ox, oy = origins[t % len(origins)]
+        assert t in best, "template %d not found" % t
+        b = best[t]
+        assert b["similarity"] == 100.0 and abs(int(b["x"]) - ox) <= 3 and abs(int(b["y"]) - oy) <= 3, (t, b, ox, oy)
+
+
+def same_list(a, b):
+    assert len(a) == len(b), (len(a), len(b))
+    for k in ("x", "y", "template_id"):
+        assert np.array_equal(a[k], b[k]), k
+    assert np.array_equal(a["similarity"].view(np.uint32), b["similarity"].view(np.uint32))
+
+
+def test_config5_2048_frames_720_templates():
+    from shape_based_matching_b200 import Detector
+
+    rng = np.random.default_rng(2048)
+    T = (4, 8)
+    h = w = 2048
+    frames = [dense_image(rng, h, w, 1, 700) for _ in range(2)]
+    orc = port.PortDetector(T, 30.0)
+    orc.process(frames[0])
+    quant = quantised_pyramid(orc, (h, w), 2)
+    origins = [(int(x) * 16, int(y) * 16) for x, y in rng.integers(1, 100, (24, 2))]
+    tdesc, feats = cut_templates(rng, quant, 720, 256, (128, 64), origins)
+    orc.add_class(tdesc, feats)
+    det = Detector(128, T, 30.0, 60.0)
+    det.setClassTemplates("c5", tdesc, feats)
+    batch = det.match_batch(frames, 90.0, ["c5"])
+    for i, f in enumerate(frames):
+        orc.process(f)
+        want = orc.match(90.0, finalize=True)
+        got = det.match_records(f, 90.0, ["c5"])
+        same_list(got, want)
+        same_list(batch[i], want)
+        if i == 0:
+            cand = det.match_candidates(f, 90.0, ["c5"])
+            same_list(cand, orc.match(90.0, finalize=False))
+            assert_found_at_origin(cand, 720, origins)
+
+
+def test_config4_4096_frame_3600_templates_8191_features():
+    from shape_based_matching_b200 import DEVICE_REC, Detector  # noqa: F401
+    from shape_based_matching_b200.sharding import merge_shard_records, shard_ids, shard_templates
+
+    import torch
+
+    rng = np.random.default_rng(4096)
+    T = (4, 8)
+    h = w = 4096
+    n_templates, nf = 3600, (8191, 4095)
+    img = dense_image(rng, h, w, 1, 5000)
+    orc = port.PortDetector(T, 30.0)
+    orc.process(img)
+    quant = quantised_pyramid(orc, (h, w), 2)
+    origins = [(int(x) * 16, int(y) * 16) for x, y in rng.integers(1, 200, (36, 2))]
+    tdesc, feats = cut_templates(rng, quant, n_templates, 768, nf, origins)
+    thr = 80.0
+
+    det = Detector(8191, T, 30.0, 60.0)
+    det.setClassTemplates("c4", tdesc, feats)
+    full_cand = det.match_candidates(img, thr, ["c4"], cap=1 << 16)
+    full = det.match_records(img, thr, ["c4"], cap=1 << 16)
+    st = det.last_stats()
+    assert st["coarse_evals"] > 5e11, st  # the configuration's scale: ~9e11 byte-adds per frame
+
+    # (b) known answers
+    assert_found_at_origin(full_cand, n_templates, origins)
+
+    # (a) oracle on a subset of the templates
+    subset = sorted(int(t) for t in rng.choice(n_templates, 5, replace=False))
+    per_t = tdesc[:, :, 4].sum(axis=1).astype(np.int64)
+    begin = np.concatenate([[0], np.cumsum(per_t)])
+    sub_tdesc = tdesc[subset]
+    sub_feats = np.concatenate([feats[begin[t] : begin[t + 1]] for t in subset])
+    orc.add_class(sub_tdesc, sub_feats)
+    want_cand = orc.match(thr, finalize=False)
+    want = orc.match(thr, finalize=True)
+    det_sub = Detector(8191, T, 30.0, 60.0)
+    det_sub.setClassTemplates("c4", sub_tdesc, sub_feats)
+    same_list(det_sub.match_candidates(img, thr, ["c4"]), want_cand)
+    same_list(det_sub.match_records(img, thr, ["c4"]), want)
+    Hc, Wc = (h >> 1) // 8, (w >> 1) // 8
+    for k in range(len(subset)):
+        assert np.array_equal(det_sub.similarity_map("c4", k, (Hc, Wc)), orc.similarity(0, k)), "raw map of template %d" % subset[k]
+    # the full run, filtered to the subset, is the same candidate list (ids mapped back)
+    pos = {t: k for k, t in enumerate(subset)}
+    sel = full_cand[np.isin(full_cand["template_id"], subset)].copy()
+    sel["template_id"] = [pos[int(t)] for t in sel["template_id"]]
+    same_list(sel, want_cand)
+
+    # (c) linearity of the raw sums: halves of one template
+    t0 = subset[0]
+    f0 = feats[begin[t0] : begin[t0 + 1]]
+    lv0, lv1 = f0[: nf[0]], f0[nf[0] :]
+    ha, hb = lv1[: nf[1] // 2], lv1[nf[1] // 2 :]
+    parts_desc = np.array([[[768, 768, 0, 0, nf[0]], [384, 384, 0, 0, len(x)]] for x in (ha, hb, lv1)], np.int32)
+    parts_feats = np.concatenate([lv0, ha, lv0, hb, lv0, lv1])
+    det_sub.setClassTemplates("c4", parts_desc, parts_feats)
+    det_sub.match_records(img, 99.0, ["c4"])
+    m = [det_sub.similarity_map("c4", k, (Hc, Wc)).astype(np.int64) for k in range(3)]
+    # template_positions is the same for the three (same width / height), so the maps add up everywhere
+    assert np.array_equal(m[0] + m[1], m[2]) and int(m[2].max()) == 4 * nf[1]
+    det_sub.close()
+
+    # (d) 8 template shards (emulated one after the other on this GPU) merge to the unsharded list
+    d_img = torch.from_numpy(img).cuda()
+    cap = 1 << 15
+    per_rank, sizes = [], []
+    for r in range(8):
+        td, ft = shard_templates(tdesc, feats, r, 8, 0)
+        sd = Detector(8191, T, 30.0, 60.0)
+        sd.setClassTemplates("c4", td, ft)
+        recs = torch.zeros(cap * DEVICE_REC.itemsize, dtype=torch.uint8, device="cuda")
+        cnt = torch.zeros(2, dtype=torch.int32, device="cuda")
+        sd.match_device(d_img.data_ptr(), w, h, 1, thr, ["c4"], d_records=recs.data_ptr(), cap=cap, d_count=cnt.data_ptr(),
+                        stream=torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        n = int(cnt.cpu()[0])
+        assert n <= cap
+        per_rank.append(recs.cpu().numpy().view(DEVICE_REC)[:n].copy())
+        sizes.append([len(shard_ids(n_templates, r, 8, 0))])
+        sd.close()
+    same_list(merge_shard_records(per_rank, sizes, 0, finalize=True), full)
+    same_list(merge_shard_records(per_rank, sizes, 0, finalize=False), full_cand)
