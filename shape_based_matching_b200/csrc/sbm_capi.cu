@@ -56,6 +56,36 @@ constexpr int SBM_SLOTS = 4;
 constexpr int COUNT_WORDS = 16; // [0..levels-1] stage counts, [10..11] u64 local evaluations
 constexpr uint32_t HEAD_RECS = 1024;
 
+// K1 tile height for a w x h level: 64x32 tiles unless that leaves the GPU under two CTAs per SM, then 64x16.
+// SBM_ORIENT_TH=8|16|32 forces one height (experiments).
+int orientTileH(int w, int h)
+{
+    static const int forced = getenv("SBM_ORIENT_TH") ? atoi(getenv("SBM_ORIENT_TH")) : 0;
+    if (forced == 8 || forced == 16 || forced == 32)
+        return forced;
+    const int cols = (w + K1_TW - 1) / K1_TW;
+    if (cols * ((h + 31) / 32) >= SBM_TALL_MIN)
+        return 32;
+    return 16; // 64x8 tiles (512 CTAs at level 1 of a 1024^2 frame) measured no faster than 64x16: 8.5 vs 8.1 us
+}
+
+void *orientFunc(int ch, int th)
+{
+    if (ch == 3)
+        return th == 32 ? (void *)k_orient<3, 32> : th == 16 ? (void *)k_orient<3, 16> : (void *)k_orient<3, 8>;
+    return th == 32 ? (void *)k_orient<1, 32> : th == 16 ? (void *)k_orient<1, 16> : (void *)k_orient<1, 8>;
+}
+
+// one K1 launch on stream st (match path: no dump outputs)
+cudaError_t launchOrient(int ch, const uint8_t *src, int w, int h, const uint8_t *mask, int mask_shift, int mask_w, float weak_sq,
+                         uint8_t *quant, cudaStream_t st)
+{
+    const int th = orientTileH(w, h);
+    float *nf = nullptr;
+    void *argv[] = {&src, &w, &h, &mask, &mask_shift, &mask_w, &weak_sq, &quant, &nf, &nf};
+    return cudaLaunchKernel(orientFunc(ch, th), dim3((w + K1_TW - 1) / K1_TW, (h + th - 1) / th), dim3(K1_THREADS), argv, 0, st);
+}
+
 struct ClassSet
 {
     int n = 0;
@@ -527,18 +557,7 @@ int enqueueFrame(sbm_ctx *c, Slot &s, const uint8_t *d_img, const uint8_t *d_mas
             src = LB.d_src;
             ++launches;
         }
-        // 64x32 tiles unless that leaves the GPU under two waves of CTAs; then 64x16
-        const bool tall = ((G.w + K1_TW - 1) / K1_TW) * ((G.h + 31) / 32) >= SBM_TALL_MIN;
-        const int th = tall ? 32 : 16;
-        dim3 g1((G.w + K1_TW - 1) / K1_TW, (G.h + th - 1) / th);
-        if (c->c == 3 && tall)
-            k_orient<3, 32><<<g1, K1_THREADS, 0, st>>>(src, G.w, G.h, d_mask, l, c->w, weak_sq, LB.d_quant, nullptr, nullptr);
-        else if (c->c == 3)
-            k_orient<3, 16><<<g1, K1_THREADS, 0, st>>>(src, G.w, G.h, d_mask, l, c->w, weak_sq, LB.d_quant, nullptr, nullptr);
-        else if (tall)
-            k_orient<1, 32><<<g1, K1_THREADS, 0, st>>>(src, G.w, G.h, d_mask, l, c->w, weak_sq, LB.d_quant, nullptr, nullptr);
-        else
-            k_orient<1, 16><<<g1, K1_THREADS, 0, st>>>(src, G.w, G.h, d_mask, l, c->w, weak_sq, LB.d_quant, nullptr, nullptr);
+        CK(launchOrient(c->c, src, G.w, G.h, d_mask, l, c->w, weak_sq, LB.d_quant, st));
         dim3 g2((G.w + K2_PW - 1) / K2_PW, (G.h + K2_PH - 1) / K2_PH);
         uint8_t *ds = c->debug ? LB.d_spread : nullptr, *dr = c->debug ? LB.d_resp : nullptr;
         if (G.T == 4)
@@ -624,13 +643,6 @@ template <typename... A> int addKernel(cudaGraph_t g, cudaGraphNode_t *node, con
     return 0;
 }
 
-void *orientFunc(int ch, bool tall)
-{
-    if (ch == 3)
-        return tall ? (void *)k_orient<3, 32> : (void *)k_orient<3, 16>;
-    return tall ? (void *)k_orient<1, 32> : (void *)k_orient<1, 16>;
-}
-
 void *spreadFunc(int T)
 {
     return T == 4 ? (void *)k_spread_linearize<4> : T == 8 ? (void *)k_spread_linearize<8> : T == 2 ? (void *)k_spread_linearize<2>
@@ -687,16 +699,15 @@ int buildGraph(sbm_ctx *c, Slot &s, const uint8_t *src0, float threshold, bool w
             dep_src.assign(1, n_pyr);
             ++launches;
         }
-        const bool tall = ((G.w + K1_TW - 1) / K1_TW) * ((G.h + 31) / 32) >= SBM_TALL_MIN;
-        const int th = tall ? 32 : 16;
+        const int th = orientTileH(G.w, G.h);
         dim3 g1((G.w + K1_TW - 1) / K1_TW, (G.h + th - 1) / th);
         cudaGraphNode_t n_or, n_sp;
         int mask_shift = l, mask_w = c->w;
-        if ((rc = addKernel(g, &n_or, dep_src, orientFunc(c->c, tall), g1, dim3(K1_THREADS), src, G.w, G.h, null_mask, mask_shift, mask_w, weak_sq,
+        if ((rc = addKernel(g, &n_or, dep_src, orientFunc(c->c, th), g1, dim3(K1_THREADS), src, G.w, G.h, null_mask, mask_shift, mask_w, weak_sq,
                             LB.d_quant, null_f, null_f)))
             return rc;
         if (l == 0)
-            s.n_orient0 = n_or, s.f_orient0 = orientFunc(c->c, tall), s.g_orient0 = g1;
+            s.n_orient0 = n_or, s.f_orient0 = orientFunc(c->c, th), s.g_orient0 = g1;
         dim3 g2((G.w + K2_PW - 1) / K2_PW, (G.h + K2_PH - 1) / K2_PH);
         const uint8_t *qin = LB.d_quant;
         if ((rc = addKernel(g, &n_sp, {n_or}, spreadFunc(G.T), g2, dim3(K2_THREADS), qin, G.w, G.h, LB.d_lm, null_dbg, null_dbg)))
@@ -1660,18 +1671,8 @@ int sbm_time_kernels(sbm_ctx *c, float threshold, int iters, float *ms, int n_ms
                 SBM_TIME(3 * l + 0, (k_pyrdown<1><<<g, K1B_THREADS, 0, st>>>(src, P.w, P.h, LB.d_src, G.w, G.h)));
             src = LB.d_src;
         }
-        const bool tall = ((G.w + K1_TW - 1) / K1_TW) * ((G.h + 31) / 32) >= SBM_TALL_MIN;
-        const int th = tall ? 32 : 16;
-        dim3 g1((G.w + K1_TW - 1) / K1_TW, (G.h + th - 1) / th);
         const uint8_t *nm = nullptr;
-        if (c->c == 3 && tall)
-            SBM_TIME(3 * l + 1, (k_orient<3, 32><<<g1, K1_THREADS, 0, st>>>(src, G.w, G.h, nm, l, c->w, weak_sq, LB.d_quant, nullptr, nullptr)));
-        else if (c->c == 3)
-            SBM_TIME(3 * l + 1, (k_orient<3, 16><<<g1, K1_THREADS, 0, st>>>(src, G.w, G.h, nm, l, c->w, weak_sq, LB.d_quant, nullptr, nullptr)));
-        else if (tall)
-            SBM_TIME(3 * l + 1, (k_orient<1, 32><<<g1, K1_THREADS, 0, st>>>(src, G.w, G.h, nm, l, c->w, weak_sq, LB.d_quant, nullptr, nullptr)));
-        else
-            SBM_TIME(3 * l + 1, (k_orient<1, 16><<<g1, K1_THREADS, 0, st>>>(src, G.w, G.h, nm, l, c->w, weak_sq, LB.d_quant, nullptr, nullptr)));
+        SBM_TIME(3 * l + 1, (void)launchOrient(c->c, src, G.w, G.h, nm, l, c->w, weak_sq, LB.d_quant, st));
         dim3 g2((G.w + K2_PW - 1) / K2_PW, (G.h + K2_PH - 1) / K2_PH);
         uint8_t *nd = nullptr;
         if (G.T == 4)
