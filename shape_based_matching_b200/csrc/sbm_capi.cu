@@ -49,7 +49,19 @@ int fail(int code, const char *fmt, ...)
             return fail(SBM_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
     } while (0)
 
-constexpr int SBM_SLOTS = 4;
+constexpr int SBM_SLOTS = 8; // frame slots a context can hold
+// frame slots the batch entry points keep in flight (SBM_FRAME_SLOTS=1..8 overrides; see profiles/ for the sweep)
+int frameSlots()
+{
+    static const int n = [] {
+        const char *e = getenv("SBM_FRAME_SLOTS");
+        if (!e)
+            e = getenv("SBM_DEVICE_SLOTS"); // older name
+        const int v = e ? atoi(e) : 6; // sweep on M1: 2 -> 41.5, 4 -> 33.2, 6 -> 31.8, 8 -> 32.1 us per frame
+        return v < 1 ? 1 : (v > SBM_SLOTS ? SBM_SLOTS : v);
+    }();
+    return n;
+}
 #ifndef SBM_TALL_MIN
 #define SBM_TALL_MIN (2 * 148)
 #endif
@@ -1192,26 +1204,27 @@ int sbm_match_batch(sbm_ctx *c, const uint8_t *const *imgs, const uint8_t *const
     frame_begin[0] = 0;
     if (n_frames == 0)
         return 0;
-    for (int k = 0; k < std::min(n_frames, SBM_SLOTS); ++k)
+    const int NS = frameSlots();
+    for (int k = 0; k < std::min(n_frames, NS); ++k)
         if ((rc = prepare(c, c->slot[k], w, h, ch, class_idx, n_classes)))
             return rc;
     const uint8_t *dm[SBM_SLOTS] = {nullptr};
     int used = 0;
     bool overflowed = false;
-    for (int i = 0; i < n_frames + SBM_SLOTS; ++i)
+    for (int i = 0; i < n_frames + NS; ++i)
     {
-        const int done = i - SBM_SLOTS; // the frame that occupied this slot before
-        Slot &s = c->slot[i % SBM_SLOTS];
+        const int done = i - NS; // the frame that occupied this slot before
+        Slot &s = c->slot[i % NS];
         if (done >= 0 && done < n_frames)
         {
-            if ((rc = finishBatchFrame(c, s, dm[i % SBM_SLOTS], threshold, true, out, cap, &used, &overflowed)))
+            if ((rc = finishBatchFrame(c, s, dm[i % NS], threshold, true, out, cap, &used, &overflowed)))
                 return rc;
             frame_begin[done + 1] = used;
         }
         if (i < n_frames)
         {
-            if ((rc = uploadFrame(s, imgs[i], w, h, ch, stride, masks ? masks[i] : nullptr, &dm[i % SBM_SLOTS])) ||
-                (rc = runFrame(c, s, s.d_frame, dm[i % SBM_SLOTS], threshold, s.stream, true)))
+            if ((rc = uploadFrame(s, imgs[i], w, h, ch, stride, masks ? masks[i] : nullptr, &dm[i % NS])) ||
+                (rc = runFrame(c, s, s.d_frame, dm[i % NS], threshold, s.stream, true)))
                 return rc;
         }
     }
@@ -1249,8 +1262,7 @@ int sbm_match_batch_device(sbm_ctx *c, const void *d_imgs, size_t frame_stride, 
     std::lock_guard<std::mutex> lock(c->mu);
     CK(cudaSetDevice(c->device));
     int rc;
-    static const int env_slots = getenv("SBM_DEVICE_SLOTS") ? atoi(getenv("SBM_DEVICE_SLOTS")) : SBM_SLOTS;
-    const int NS = std::max(1, std::min(env_slots, SBM_SLOTS));
+    const int NS = frameSlots();
     const int ns = std::min(n_frames, NS);
     for (int k = 0; k < ns; ++k)
         if ((rc = prepare(c, c->slot[k], w, h, ch, class_idx, n_classes)))

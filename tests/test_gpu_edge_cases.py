@@ -1,0 +1,176 @@
+"""Edge cases of Detector::match on the GPU: the reference's asserts and limits (line2Dup.cpp:639, :751-752, :811,
+:1195), unknown and multiple classes (:1124-1138), empty inputs, masks that remove everything, templates larger
+than the frame (template_positions <= 0, :825), capacity growth, and shape changes on a live context.  Expectations
+come from the CPU restatement (oracle/sbm_oracle.cpp) wherever there is something to compare."""
+import numpy as np
+import pytest
+
+from oracle import port
+from test_gpu_vs_port import synth_image, synth_templates
+
+pytestmark = pytest.mark.gpu
+
+
+def same_list(a, b):
+    assert len(a) == len(b), (len(a), len(b))
+    for k in ("x", "y", "template_id", "class_idx"):
+        assert np.array_equal(a[k], b[k]), k
+    assert np.array_equal(a["similarity"].view(np.uint32), b["similarity"].view(np.uint32))
+
+
+def make(rng, h=128, w=160, c=3, T=(4, 8), n=8, box=(40, 36), nf=24):
+    from shape_based_matching_b200 import Detector
+
+    img = synth_image(rng, h, w, c)
+    tdesc, feats = synth_templates(rng, n, len(T), box, nf)
+    det = Detector(nf, T, 30.0, 60.0)
+    det.setClassTemplates("a", tdesc, feats)
+    orc = port.PortDetector(T, 30.0)
+    orc.add_class(tdesc, feats)
+    return det, orc, img, tdesc, feats
+
+
+def test_frame_shapes_the_reference_asserts_on():
+    from shape_based_matching_b200 import SbmError
+
+    rng = np.random.default_rng(1)
+    det, _orc, _img, _td, _ft = make(rng)
+    for shape in ((100, 100, 3), (128, 164, 3), (72, 128, 1)):  # level-1 rows/cols not a multiple of T = 8
+        with pytest.raises(SbmError) as e:
+            det.match_records(np.zeros(shape, np.uint8), 50.0, ["a"])
+        assert e.value.code == -1
+    with pytest.raises(SbmError):
+        det.match_records(np.zeros((128, 160, 2), np.uint8), 50.0, ["a"])  # 1 or 3 channels only
+    with pytest.raises(SbmError):
+        det.match_records(np.zeros((128, 160, 3), np.uint8), 50.0, ["a"], masks=np.zeros((64, 160), np.uint8))
+    # the context is still usable afterwards
+    assert isinstance(det.match_records(np.zeros((128, 160, 3), np.uint8), 50.0, ["a"]), np.ndarray)
+
+
+def test_feature_count_limit_8191():
+    from shape_based_matching_b200 import Detector, SbmError
+
+    rng = np.random.default_rng(2)
+    img = synth_image(rng, 256, 256, 1)
+    for nf, ok in ((8191, True), (8192, False)):
+        tdesc = np.array([[[200, 200, 0, 0, nf]]], np.int32)
+        feats = np.stack([rng.integers(0, 200, nf), rng.integers(0, 200, nf), rng.integers(0, 8, nf)], 1).astype(np.int32)
+        det = Detector(nf, (4,), 30.0, 60.0)
+        det.setClassTemplates("big", tdesc, feats)
+        if ok:
+            orc = port.PortDetector((4,), 30.0)
+            orc.add_class(tdesc, feats)
+            orc.process(img)
+            same_list(det.match_records(img, 20.0, ["big"]), orc.match(20.0))
+            assert np.array_equal(det.similarity_map("big", 0, (64, 64)), orc.similarity(0, 0))
+        else:
+            with pytest.raises(SbmError) as e:  # CV_Error "feature size too large" (line2Dup.cpp:1195)
+                det.match_records(img, 20.0, ["big"])
+            assert e.value.code == -1
+
+
+def test_unknown_empty_and_multiple_classes():
+    from shape_based_matching_b200 import Detector
+
+    rng = np.random.default_rng(3)
+    T = (4, 8)
+    img = synth_image(rng, 128, 160, 3)
+    ta, fa = synth_templates(rng, 6, 2, (40, 36), 24)
+    tb, fb = synth_templates(rng, 5, 2, (30, 44), 30)
+    det = Detector(30, T, 30.0, 60.0)
+    assert len(det.match_records(img, 30.0)) == 0  # no templates at all
+    det.setClassTemplates("b_second", tb, fb)
+    det.setClassTemplates("a_first", ta, fa)
+    orc = port.PortDetector(T, 30.0)
+    orc.add_class(ta, fa)  # class slots follow std::map order: "a_first" < "b_second"
+    orc.add_class(tb, fb)
+    orc.process(img)
+    both = det.match_records(img, 30.0)  # empty list = all classes in map order (line2Dup.cpp:1124-1130)
+    same_list(both, orc.match(30.0, class_idx=(0, 1)))
+    assert set(both["class_idx"]) == {0, 1}
+    assert len(det.match_records(img, 30.0, ["nope"])) == 0  # unknown ids are skipped (:1136-1138)
+    only_b = det.match_records(img, 30.0, ["nope", "b_second"])
+    want_b = orc.match(30.0, class_idx=(1,))
+    assert len(only_b) == len(want_b) and np.array_equal(only_b["x"], want_b["x"]) and np.array_equal(only_b["template_id"], want_b["template_id"])
+    assert [m.class_id for m in det.match(img, 30.0, ["b_second"])][:1] in ([], ["b_second"])
+    # caller's order matters for the candidate order: b before a
+    same_list(det.match_candidates(img, 30.0, ["b_second", "a_first"]), orc.match(30.0, class_idx=(1, 0), finalize=False))
+    # removing a class
+    det.setClassTemplates("a_first", ta[:0], fa[:0])
+    assert set(det.match_records(img, 30.0)["class_idx"]) <= {0, 1}
+
+
+def test_thresholds_and_capacity_growth():
+    rng = np.random.default_rng(4)
+    det, orc, img, _td, _ft = make(rng)
+    orc.process(img)
+    assert len(det.match_records(img, 100.5, ["a"])) == 0
+    lots = orc.match(1.0)
+    assert len(lots) > 50
+    same_list(det.match_records(img, 1.0, ["a"], cap=4), lots)  # tiny output buffer: grown, not truncated
+    same_list(det.match_candidates(img, 1.0, ["a"], cap=4), orc.match(1.0, finalize=False))
+    same_list(det.match_records(img, 40.0, ["a"]), orc.match(40.0))  # and back to a selective threshold
+
+
+def test_masks():
+    rng = np.random.default_rng(5)
+    det, orc, img, _td, _ft = make(rng)
+    h, w = img.shape[:2]
+    zero = np.zeros((h, w), np.uint8)
+    orc.process(img, zero)
+    assert len(orc.match(5.0)) == 0
+    assert len(det.match_records(img, 5.0, ["a"], masks=zero)) == 0
+    assert not det.intermediate(0, 0).any()
+    stripes = np.zeros((h, w), np.uint8)
+    stripes[:, ::3] = 7  # any non-zero value keeps the pixel (copyTo(dst, mask), line2Dup.cpp:446-450)
+    orc.process(img, stripes)
+    same_list(det.match_records(img, 20.0, ["a"], masks=stripes), orc.match(20.0))
+    full = np.full((h, w), 255, np.uint8)
+    orc.process(img)
+    same_list(det.match_records(img, 30.0, ["a"], masks=full), orc.match(30.0))
+
+
+def test_templates_larger_than_the_frame_and_features_outside():
+    from shape_based_matching_b200 import Detector
+
+    rng = np.random.default_rng(6)
+    T = (4, 8)
+    img = synth_image(rng, 64, 96, 3)
+    # template 0: bigger than the frame at both levels (template_positions <= 0); template 1: fits, but some of its
+    # features lie outside the coarse image and are skipped (line2Dup.cpp:836); template 2: ordinary
+    tdesc = np.array([[[400, 300, 0, 0, 20], [200, 150, 0, 0, 10]],
+                      [[60, 40, 0, 0, 20], [30, 20, 0, 0, 10]],
+                      [[30, 30, 0, 0, 20], [15, 15, 0, 0, 10]]], np.int32)
+    feats = []
+    for t in range(3):
+        for l in range(2):
+            bw, bh, nf = int(tdesc[t, l, 0]), int(tdesc[t, l, 1]), int(tdesc[t, l, 4])
+            f = np.stack([rng.integers(0, bw + 1, nf), rng.integers(0, bh + 1, nf), rng.integers(0, 8, nf)], 1)
+            if t == 1:
+                f[:3, 0] += 500  # far outside the frame
+            feats.append(f)
+    feats = np.concatenate(feats).astype(np.int32)
+    det = Detector(20, T, 30.0, 60.0)
+    det.setClassTemplates("c", tdesc, feats)
+    orc = port.PortDetector(T, 30.0)
+    orc.add_class(tdesc, feats)
+    orc.process(img)
+    for thr in (10.0, 35.0):
+        same_list(det.match_candidates(img, thr, ["c"]), orc.match(thr, finalize=False))
+        same_list(det.match_records(img, thr, ["c"]), orc.match(thr))
+    for t in range(3):
+        assert np.array_equal(det.similarity_map("c", t, (4, 6)), orc.similarity(0, t)), t
+
+
+def test_shape_changes_on_a_live_context():
+    rng = np.random.default_rng(7)
+    det, orc, _img, _td, _ft = make(rng)
+    for shape in ((128, 160, 3), (256, 192, 3), (64, 64, 1), (128, 160, 3), (256, 192, 1)):
+        img = synth_image(rng, *shape)
+        orc.process(img)
+        same_list(det.match_records(img, 30.0, ["a"]), orc.match(30.0))
+        frames = [img, np.ascontiguousarray(img[::-1]), img]
+        got = det.match_batch(frames, 30.0, ["a"])
+        for f, g in zip(frames, got):
+            orc.process(f)
+            same_list(g, orc.match(30.0))
