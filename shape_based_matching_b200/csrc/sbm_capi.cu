@@ -281,14 +281,22 @@ int ensureShape(sbm_ctx *c, int w, int h, int ch)
     return 0;
 }
 
-int ensureSlot(sbm_ctx *c, Slot &s)
+// the slot's stream and its events are created together (the timers rely on the events)
+int ensureStream(Slot &s)
 {
     if (!s.stream)
-    {
         CK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
-        for (int i = 0; i < 4; ++i)
+    for (int i = 0; i < 4; ++i)
+        if (!s.ev[i])
             CK(cudaEventCreate(&s.ev[i]));
-    }
+    return 0;
+}
+
+int ensureSlot(sbm_ctx *c, Slot &s)
+{
+    int rc0;
+    if ((rc0 = ensureStream(s)))
+        return rc0;
     if (s.shape_gen != c->shape_gen || (c->debug && !s.debug_bufs))
     {
         freeSlotShape(s);
@@ -1599,6 +1607,9 @@ int sbm_time_l2_read(sbm_ctx *c, size_t bytes, int iters, float *gb_per_s)
     std::lock_guard<std::mutex> lock(c->mu);
     CK(cudaSetDevice(c->device));
     Slot &s = c->slot[0];
+    int rc_s;
+    if ((rc_s = ensureStream(s)))
+        return rc_s;
     const uint32_t n_vec = (uint32_t)(bytes / 16 / 1024 * 1024); // whole 1024-vector rounds only
     if (n_vec == 0)
         return fail(SBM_ERR_BAD_ARG, "buffer too small");
@@ -1746,8 +1757,9 @@ int sbm_quantized_orientations(sbm_ctx *c, const uint8_t *img, int w, int h, int
     std::lock_guard<std::mutex> lock(c->mu);
     CK(cudaSetDevice(c->device));
     Slot &s = c->slot[0];
-    if (!s.stream)
-        CK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+    int rc_s;
+    if ((rc_s = ensureStream(s)))
+        return rc_s;
     cudaStream_t st = s.stream;
     const size_t row = (size_t)w * ch;
     uint8_t *d_a = nullptr, *d_b = nullptr, *d_q = nullptr;
