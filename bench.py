@@ -40,7 +40,8 @@ THRESHOLD = 90.0
 W = H = 1024
 C = 3
 N_TEMPLATES = 360
-REC_CAP = 4096  # per-frame record capacity of the device-resident path
+REC_CAP = 512  # per-frame record capacity of the device-resident path = the all_gather payload (20 B each); M1 frames
+# produce ~100 records; the counts are checked after the timed region, an overflow aborts the run
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE k_similarity launch on this workload, from the committed
 # `ncu --set full` capture (profiles/r1c_summary.md); bench.py itself never runs under a profiler
 K_SIMILARITY_DRAM_BYTES = 2244096
@@ -290,6 +291,9 @@ def main():
     e1.record(stream)
     barrier()
     ms = e0.elapsed_time(e1)
+    max_recs = int(d_cnt[:, 0].max().item())
+    if max_recs > REC_CAP:
+        raise SystemExit("bench.py: a frame produced %d records, more than REC_CAP=%d: exchanged lists were truncated" % (max_recs, REC_CAP))
     t = torch.tensor([ms, float(evals_step_rank)], dtype=torch.float64, device=dev)
     if world > 1:
         tm = t.clone()
@@ -457,7 +461,8 @@ def main():
         "config": {"workload": "M1: 1024x1024x3 frames x 360 templates (case1 ids 0..359, 131/71 features, T={4,8}, thr 90)",
                    "frames_per_step_per_gpu": B, "sharding": "frames (each rank its own frames, all templates)",
                    "l2_policy": "inputs larger than L2: %d MiB of distinct frames per step per GPU" % (B * W * H * C >> 20),
-                   "evals_per_frame": evals_step / (B * world), "final_matches_per_step": n_final // max(1, args.steps)},
+                   "evals_per_frame": evals_step / (B * world), "final_matches_per_step": n_final // max(1, args.steps),
+                   "records_per_frame_max": max_recs, "exchange_bytes_per_rank_per_step": (B * (REC_CAP * rec_bytes + 8)) if world > 1 else 0},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": B * W * H * C, "d2h_bytes_per_step": d2h,
                 "ms_per_frame": e2e_s / B * 1e3, "api": "Detector.match_batch(64 pinned host frames) -> 64 final host lists"},
         "latency": {"device_ms_per_frame_single_stream": serial_ms_per_frame, "match_call_ms_host_to_host": single_call_ms},
