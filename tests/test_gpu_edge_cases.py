@@ -174,3 +174,31 @@ def test_shape_changes_on_a_live_context():
         for f, g in zip(frames, got):
             orc.process(f)
             same_list(g, orc.match(30.0))
+
+
+@pytest.mark.parametrize("shape,T", [((32, 32, 1), (4, 8)), ((32, 48, 3), (4, 8)), ((16, 16, 3), (4,)), ((8, 64, 1), (2, 4))])
+def test_frames_smaller_than_a_kernel_tile(shape, T):
+    """frames far smaller than any kernel tile: every intermediate, every raw similarity map and the (usually empty)
+    lists still equal the restatement's"""
+    from shape_based_matching_b200 import Detector
+
+    rng = np.random.default_rng(sum(shape) + len(T))
+    img = (rng.integers(0, 256, shape, dtype=np.uint8) // 4).astype(np.uint8)
+    img[shape[0] // 4 : shape[0] // 2 + 2, shape[1] // 3 : shape[1] // 3 * 2] = 230  # one bright block: strong edges
+    tdesc, feats = synth_templates(rng, 4, len(T), (10, 6), 8)
+    det = Detector(8, T, 30.0, 60.0)
+    det.setClassTemplates("s", tdesc, feats)
+    det.set_debug(True)
+    orc = port.PortDetector(T, 30.0)
+    orc.add_class(tdesc, feats)
+    orc.process(img)
+    for thr in (1.0, 30.0):
+        same_list(det.match_candidates(img, thr, ["s"]), orc.match(thr, finalize=False))
+        same_list(det.match_records(img, thr, ["s"]), orc.match(thr))
+    for l in range(len(T)):
+        for kind in range(4):
+            assert np.array_equal(det.intermediate(l, kind), orc.get(l, kind)), (l, kind)
+    lv = len(T) - 1
+    hw = ((shape[0] >> lv) // T[lv], (shape[1] >> lv) // T[lv])
+    for t in range(4):
+        assert np.array_equal(det.similarity_map("s", t, hw), orc.similarity(0, t)), t

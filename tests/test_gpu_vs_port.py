@@ -46,6 +46,9 @@ CONFIGS = [
     (256, 192, 3, (4, 4, 8), 8, (64, 48), 40, 30.0, False),  # three pyramid levels
     (192, 320, 3, (8, 8), 5, (100, 60), 200, 30.0, False),   # wide template, many features
     (64, 64, 3, (2, 4), 4, (16, 16), 12, 30.0, False),       # T = 2 at level 0 (rows not a multiple of 4 bytes * 3)
+    (64, 66, 3, (2,), 4, (20, 16), 16, 30.0, False),         # width not a multiple of 4: unaligned rows everywhere
+    (48, 70, 1, (2,), 4, (20, 16), 16, 30.0, True),          # same, one channel, masked
+    (192, 208, 3, (4, 8), 6, (60, 50), 50, 30.0, False),     # width not a multiple of the 64 / 128 pixel kernel tiles
 ]
 
 
