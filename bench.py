@@ -393,6 +393,18 @@ def main():
         det.match_records(pin_np[i], THRESHOLD, [cid])
     single_call_ms = (time.perf_counter() - t0) / B * 1e3
     d2h = (16 * 4 + 1024 * rec_bytes) * B  # counters + head of the record buffer, per frame
+    # the floor under e2e: the same B pinned frames copied host -> device back to back and nothing else
+    d_sink = torch.empty((B, H, W, C), dtype=torch.uint8, device=dev)
+    h2d_best = None
+    for _ in range(3):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for i in range(B):
+            d_sink[i].copy_(pinned[i], non_blocking=True)
+        torch.cuda.synchronize()
+        dt_ = time.perf_counter() - t0
+        h2d_best = dt_ if h2d_best is None else min(h2d_best, dt_)
+    h2d_us_per_frame = h2d_best / B * 1e6
     clocks = sampler.stop() if rank == 0 else None
 
     if rank != 0:
@@ -464,7 +476,10 @@ def main():
                    "evals_per_frame": evals_step / (B * world), "final_matches_per_step": n_final // max(1, args.steps),
                    "records_per_frame_max": max_recs, "exchange_bytes_per_rank_per_step": (B * (REC_CAP * rec_bytes + 8)) if world > 1 else 0},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": B * W * H * C, "d2h_bytes_per_step": d2h,
-                "ms_per_frame": e2e_s / B * 1e3, "api": "Detector.match_batch(64 pinned host frames) -> 64 final host lists"},
+                "ms_per_frame": e2e_s / B * 1e3, "api": "Detector.match_batch(64 pinned host frames) -> 64 final host lists",
+                "pcie_floor": {"h2d_us_per_frame": h2d_us_per_frame, "h2d_GBps": W * H * C / (h2d_us_per_frame * 1e-6) / 1e9,
+                               "e2e_over_floor": (e2e_s / B * 1e6) / h2d_us_per_frame,
+                               "how": "the step's pinned frames copied host -> device back to back on one stream, best of 3 (this rank alone)"}},
         "latency": {"device_ms_per_frame_single_stream": serial_ms_per_frame, "match_call_ms_host_to_host": single_call_ms},
         "gpu_launches": launches_per_frame * B * args.steps,
         "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline,
