@@ -479,7 +479,7 @@ def main():
                 "ms_per_frame": e2e_s / B * 1e3, "api": "Detector.match_batch(64 pinned host frames) -> 64 final host lists",
                 "pcie_floor": {"h2d_us_per_frame": h2d_us_per_frame, "h2d_GBps": W * H * C / (h2d_us_per_frame * 1e-6) / 1e9,
                                "e2e_over_floor": (e2e_s / B * 1e6) / h2d_us_per_frame,
-                               "how": "the step's pinned frames copied host -> device back to back on one stream, best of 3 (this rank alone)"}},
+                               "how": "the step's pinned frames copied host -> device back to back on one stream, best of 3; under torchrun every rank does this at the same time, so the floor includes the contention for the host"}},
         "latency": {"device_ms_per_frame_single_stream": serial_ms_per_frame, "match_call_ms_host_to_host": single_call_ms},
         "gpu_launches": launches_per_frame * B * args.steps,
         "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline,
