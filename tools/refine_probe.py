@@ -5,6 +5,9 @@ from _fixtures import load_case, load_templates
 from shape_based_matching_b200 import Detector
 case = load_case("m1")
 cid, tdesc, feats, nf = load_templates("case1[:360]")
+import shape_based_matching_b200._capi as capi
+if len(sys.argv) > 1:
+    capi.LIB_PATH = sys.argv[1]
 det = Detector(nf, (4, 8)); det.setClassTemplates(cid, tdesc, feats)
 for thr in (99.9, 98.0, 95.0, 90.0, 85.0, 80.0, 70.0):
     det.match_records(case["img"], thr, [cid], cap=1 << 16)
