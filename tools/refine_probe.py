@@ -9,7 +9,7 @@ import shape_based_matching_b200._capi as capi
 if len(sys.argv) > 1:
     capi.LIB_PATH = sys.argv[1]
 det = Detector(nf, (4, 8)); det.setClassTemplates(cid, tdesc, feats)
-for thr in (99.9, 98.0, 95.0, 90.0, 85.0, 80.0, 70.0):
+for thr in (100.5, 99.9, 98.0, 95.0, 90.0, 85.0, 80.0, 70.0):
     det.match_records(case["img"], thr, [cid], cap=1 << 16)
     st = det.last_stats()
     t = det.time_kernels(thr, 20)
