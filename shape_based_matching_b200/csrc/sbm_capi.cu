@@ -272,13 +272,33 @@ int ensureShape(sbm_ctx *c, int w, int h, int ch)
         G.lm_bytes = 8 * px;
         // tail slack: flat addressing lets the last memory be over-read: a whole memory for the
         // coarse scan past template_positions, 16 rows + 16 for the local patch, + the realigning vector loads
-        G.lm_alloc = G.lm_bytes + std::max(WH, (size_t)16 * G.W + 16) + 128;
+        // (K5a runs whole warps: up to 31 lanes x 16 positions beyond the last reported one)
+        G.lm_alloc = G.lm_bytes + std::max(WH, (size_t)16 * G.W + 16) + 1024;
     }
     c->w = w, c->h = h, c->c = ch;
     ++c->shape_gen;
     ++c->epoch;
     c->coarse_dirty = true;
     return 0;
+}
+
+// K5b walks the candidate list grid-stride with a static split, so the grid is exactly the number of CTAs that are
+// resident at once (a CTA that starts after the others have finished would do its whole share alone)
+int refineGrid()
+{
+    static int grid = 0;
+    if (!grid)
+    {
+        int dev = 0, sms = 148, per_sm = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_refine, K6_THREADS, 0) != cudaSuccess || per_sm < 1)
+            per_sm = 1;
+        if (const char *e = getenv("SBM_REFINE_CTAS_PER_SM"))
+            per_sm = std::max(1, atoi(e));
+        grid = sms * per_sm;
+    }
+    return grid;
 }
 
 // the slot's stream and its events are created together (the timers rely on the events)
@@ -621,7 +641,7 @@ int enqueueFrame(sbm_ctx *c, Slot &s, const uint8_t *d_img, const uint8_t *d_mas
         out_cnt = (last && user_count) ? user_count : s.d_counts + stage;
         if (c->n_active > 0)
         {
-            k_refine<<<148 * 4, K6_THREADS, 0, st>>>(s.lv[l].d_lm, c->tl[l].d_tl, c->tl[l].d_feats, in, in_cnt, in_cap, out, out_cnt, out_cap,
+            k_refine<<<refineGrid(), K6_THREADS, 0, st>>>(s.lv[l].d_lm, c->tl[l].d_tl, c->tl[l].d_feats, in, in_cnt, in_cap, out, out_cnt, out_cap,
                                                      G.w, G.h, G.T, threshold, nullptr, 0,
                                                      reinterpret_cast<unsigned long long *>(s.d_counts + 10));
             ++launches;
@@ -774,7 +794,7 @@ int buildGraph(sbm_ctx *c, Slot &s, const uint8_t *src0, float threshold, bool w
             int raw_center = 0;
             unsigned long long *ev = reinterpret_cast<unsigned long long *>(s.d_counts + 10);
             cudaGraphNode_t n_ref;
-            if ((rc = addKernel(g, &n_ref, {tail, spread_node[l]}, (void *)k_refine, dim3(148 * 4), dim3(K6_THREADS), lm, tl, ff, cin, cin_cnt, in_cap,
+            if ((rc = addKernel(g, &n_ref, {tail, spread_node[l]}, (void *)k_refine, dim3(refineGrid()), dim3(K6_THREADS), lm, tl, ff, cin, cin_cnt, in_cap,
                                 out, out_cnt, out_cap, G.w, G.h, G.T, threshold, nodump, raw_center, ev)))
                 return rc;
             tail = n_ref;
@@ -1722,7 +1742,7 @@ int sbm_time_kernels(sbm_ctx *c, float threshold, int iters, float *ms, int n_ms
     {
         const LevelGeom &G = c->geom[l];
         if (stage == 1)
-            SBM_TIME(3 * L + stage, (k_refine<<<148 * 4, K6_THREADS, 0, st>>>(s.lv[l].d_lm, c->tl[l].d_tl, c->tl[l].d_feats, s.d_buf[0], s.d_counts + 0,
+            SBM_TIME(3 * L + stage, (k_refine<<<refineGrid(), K6_THREADS, 0, st>>>(s.lv[l].d_lm, c->tl[l].d_tl, c->tl[l].d_feats, s.d_buf[0], s.d_counts + 0,
                                                                               s.cap, s.d_buf[1], d_tmp + 1, 0u, G.w, G.h, G.T, threshold, nullptr, 0,
                                                                               reinterpret_cast<unsigned long long *>(d_tmp + 10))));
     }
@@ -1812,3 +1832,19 @@ int sbm_quantized_orientations(sbm_ctx *c, const uint8_t *img, int w, int h, int
     return 0;
 }
 }
+
+#ifdef SBM_TRACE
+// experiments only (tools/stage_trace.py): the per-stage clock sums of K5a / K5b, optionally cleared
+extern "C" int sbm_trace_read(unsigned long long *out16, int reset)
+{
+    if (out16 && cudaMemcpyFromSymbol(out16, sbm::g_trace, sizeof(unsigned long long) * 16) != cudaSuccess)
+        return -1;
+    if (reset)
+    {
+        unsigned long long z[16] = {0};
+        if (cudaMemcpyToSymbol(sbm::g_trace, z, sizeof(z)) != cudaSuccess)
+            return -1;
+    }
+    return 0;
+}
+#endif
