@@ -43,8 +43,8 @@ N_TEMPLATES = 360
 REC_CAP = 512  # per-frame record capacity of the device-resident path = the all_gather payload (20 B each); M1 frames
 # produce ~100 records; the counts are checked after the timed region, an overflow aborts the run
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE k_similarity launch on this workload, from the committed
-# `ncu --set full` capture (profiles/r1c_summary.md); bench.py itself never runs under a profiler
-K_SIMILARITY_DRAM_BYTES = 2244096
+# `ncu --set full` capture (profiles/r1z_summary.md); bench.py itself never runs under a profiler
+K_SIMILARITY_DRAM_BYTES = 2288384
 
 
 def load_workload():
@@ -426,7 +426,7 @@ def main():
     roofline = {
         "kernel": "k_similarity", "bound": "hbm", "achieved": sim_gbs, "peak": hbm_peak, "unit": "GB/s",
         "frac": sim_gbs / hbm_peak, "traffic": K_SIMILARITY_DRAM_BYTES,
-        "traffic_source": "profiles/r1c_summary.md (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum, one launch)",
+        "traffic_source": "profiles/r1z_summary.md (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum, one launch)",
         "peak_source": peak_src,
         "algorithmic_bytes_per_launch": coarse, "avg_launch_ms": sim_ms,
         "l2": {"read_peak_gbs": l2_gbs, "frac": sim_gbs / l2_gbs, "working_set_bytes": lm_bytes,
