@@ -110,6 +110,7 @@ struct LevelGeom
 {
     int T = 0, w = 0, h = 0, W = 0, H = 0;
     size_t lm_bytes = 0, lm_alloc = 0;
+    bool nib = false; // memories packed two responses per byte (the coarsest level when W is even): k_similarity_nib reads them
 };
 
 // templates of one pyramid level on the device
@@ -253,6 +254,16 @@ int checkShape(sbm_ctx *c, int w, int h, int ch)
 }
 
 // frame shape -> level geometry (no allocation; slots follow lazily through shape_gen)
+// SBM_COARSE_NIBBLES=0 keeps one byte per response at the coarsest level too (the layout of every other level)
+bool coarseNibbles()
+{
+    static const bool on = [] {
+        const char *e = getenv("SBM_COARSE_NIBBLES");
+        return !(e && atoi(e) == 0);
+    }();
+    return on;
+}
+
 int ensureShape(sbm_ctx *c, int w, int h, int ch)
 {
     if (c->w == w && c->h == h && c->c == ch && !c->geom.empty())
@@ -274,6 +285,7 @@ int ensureShape(sbm_ctx *c, int w, int h, int ch)
         // coarse scan past template_positions, 16 rows + 16 for the local patch, + the realigning vector loads
         // (K5a runs whole warps: up to 31 lanes x 16 positions beyond the last reported one)
         G.lm_alloc = G.lm_bytes + std::max(WH, (size_t)16 * G.W + 16) + 1024;
+        G.nib = l == c->levels - 1 && (G.W & 1) == 0 && coarseNibbles();
     }
     c->w = w, c->h = h, c->c = ch;
     ++c->shape_gen;
@@ -559,6 +571,10 @@ int ensureActive(sbm_ctx *c, const int *class_idx, int n_classes)
 }
 
 // everything a match call needs before it can enqueue on slot s
+cudaError_t launchSpread(const LevelGeom &G, const uint8_t *quant, uint8_t *lm, uint8_t *dbg_spread, uint8_t *dbg_resp, cudaStream_t st);
+cudaError_t launchSimilarity(bool nib, dim3 grid, const uint8_t *lm, const uint32_t *coff, const TemplCoarse *tc, const uint32_t *active, int W,
+                             int HW, int T, float threshold, Cand *out, uint32_t *counter, uint32_t cap, uint16_t *dump, cudaStream_t st);
+
 int prepare(sbm_ctx *c, Slot &s, int w, int h, int ch, const int *class_idx, int n_classes)
 {
     int rc;
@@ -598,16 +614,8 @@ int enqueueFrame(sbm_ctx *c, Slot &s, const uint8_t *d_img, const uint8_t *d_mas
             ++launches;
         }
         CK(launchOrient(c->c, src, G.w, G.h, d_mask, l, c->w, weak_sq, LB.d_quant, st));
-        dim3 g2((G.w + K2_PW - 1) / K2_PW, (G.h + K2_PH - 1) / K2_PH);
         uint8_t *ds = c->debug ? LB.d_spread : nullptr, *dr = c->debug ? LB.d_resp : nullptr;
-        if (G.T == 4)
-            k_spread_linearize<4><<<g2, K2_THREADS, 0, st>>>(LB.d_quant, G.w, G.h, LB.d_lm, ds, dr);
-        else if (G.T == 8)
-            k_spread_linearize<8><<<g2, K2_THREADS, 0, st>>>(LB.d_quant, G.w, G.h, LB.d_lm, ds, dr);
-        else if (G.T == 2)
-            k_spread_linearize<2><<<g2, K2_THREADS, 0, st>>>(LB.d_quant, G.w, G.h, LB.d_lm, ds, dr);
-        else
-            k_spread_linearize<16><<<g2, K2_THREADS, 0, st>>>(LB.d_quant, G.w, G.h, LB.d_lm, ds, dr);
+        CK(launchSpread(G, LB.d_quant, LB.d_lm, ds, dr, st));
         launches += 2;
     }
     if (c->timing)
@@ -622,8 +630,8 @@ int enqueueFrame(sbm_ctx *c, Slot &s, const uint8_t *d_img, const uint8_t *d_mas
     if (c->n_active > 0)
     {
         dim3 g(c->n_active, (HW + K5_TILE - 1) / K5_TILE);
-        k_similarity<<<g, K5_THREADS, 0, st>>>(s.lv[L - 1].d_lm, c->d_coff, c->d_tcoarse, c->d_active, CG.W, HW, CG.T, threshold, out,
-                                               out_cnt, out_cap, nullptr);
+        CK(launchSimilarity(CG.nib, g, s.lv[L - 1].d_lm, c->d_coff, c->d_tcoarse, c->d_active, CG.W, HW, CG.T, threshold, out, out_cnt, out_cap,
+                            nullptr, st));
         ++launches;
     }
     if (c->timing)
@@ -683,10 +691,31 @@ template <typename... A> int addKernel(cudaGraph_t g, cudaGraphNode_t *node, con
     return 0;
 }
 
-void *spreadFunc(int T)
+void *spreadFunc(int T, bool nib)
 {
+    if (nib)
+        return T == 4 ? (void *)k_spread_linearize<4, true> : T == 8 ? (void *)k_spread_linearize<8, true>
+               : T == 2 ? (void *)k_spread_linearize<2, true> : (void *)k_spread_linearize<16, true>;
     return T == 4 ? (void *)k_spread_linearize<4> : T == 8 ? (void *)k_spread_linearize<8> : T == 2 ? (void *)k_spread_linearize<2>
                                                                                                      : (void *)k_spread_linearize<16>;
+}
+
+void *similarityFunc(bool nib) { return nib ? (void *)k_similarity_nib : (void *)k_similarity; }
+
+cudaError_t launchSpread(const LevelGeom &G, const uint8_t *quant, uint8_t *lm, uint8_t *dbg_spread, uint8_t *dbg_resp, cudaStream_t st)
+{
+    dim3 g2((G.w + K2_PW - 1) / K2_PW, (G.h + K2_PH - 1) / K2_PH);
+    int w = G.w, h = G.h;
+    void *argv[] = {(void *)&quant, (void *)&w, (void *)&h, (void *)&lm, (void *)&dbg_spread, (void *)&dbg_resp};
+    return cudaLaunchKernel(spreadFunc(G.T, G.nib), g2, dim3(K2_THREADS), argv, 0, st);
+}
+
+cudaError_t launchSimilarity(bool nib, dim3 grid, const uint8_t *lm, const uint32_t *coff, const TemplCoarse *tc, const uint32_t *active, int W,
+                             int HW, int T, float threshold, Cand *out, uint32_t *counter, uint32_t cap, uint16_t *dump, cudaStream_t st)
+{
+    void *argv[] = {(void *)&lm,        (void *)&coff, (void *)&tc,      (void *)&active, (void *)&W,   (void *)&HW,
+                    (void *)&T,         (void *)&threshold, (void *)&out, (void *)&counter, (void *)&cap, (void *)&dump};
+    return cudaLaunchKernel(similarityFunc(nib), grid, dim3(K5_THREADS), argv, 0, st);
 }
 
 int buildGraph(sbm_ctx *c, Slot &s, const uint8_t *src0, float threshold, bool with_fetch)
@@ -750,7 +779,7 @@ int buildGraph(sbm_ctx *c, Slot &s, const uint8_t *src0, float threshold, bool w
             s.n_orient0 = n_or, s.f_orient0 = orientFunc(c->c, th), s.g_orient0 = g1;
         dim3 g2((G.w + K2_PW - 1) / K2_PW, (G.h + K2_PH - 1) / K2_PH);
         const uint8_t *qin = LB.d_quant;
-        if ((rc = addKernel(g, &n_sp, {n_or}, spreadFunc(G.T), g2, dim3(K2_THREADS), qin, G.w, G.h, LB.d_lm, null_dbg, null_dbg)))
+        if ((rc = addKernel(g, &n_sp, {n_or}, spreadFunc(G.T, G.nib), g2, dim3(K2_THREADS), qin, G.w, G.h, LB.d_lm, null_dbg, null_dbg)))
             return rc;
         spread_node[l] = n_sp;
         launches += 2;
@@ -770,7 +799,7 @@ int buildGraph(sbm_ctx *c, Slot &s, const uint8_t *src0, float threshold, bool w
         const TemplCoarse *tc = c->d_tcoarse;
         uint16_t *nodump = nullptr;
         cudaGraphNode_t n_sim;
-        if ((rc = addKernel(g, &n_sim, {n_memset, spread_node[L - 1]}, (void *)k_similarity, gs, dim3(K5_THREADS), lm, coff, tc, act, CG.W, HW, CG.T,
+        if ((rc = addKernel(g, &n_sim, {n_memset, spread_node[L - 1]}, similarityFunc(CG.nib), gs, dim3(K5_THREADS), lm, coff, tc, act, CG.W, HW, CG.T,
                             threshold, in, in_cnt, in_cap, nodump)))
             return rc;
         tail = n_sim;
@@ -1482,6 +1511,16 @@ int sbm_get_intermediate(sbm_ctx *c, int level, int kind, void *dst, size_t byte
     if (bytes != need)
         return fail(SBM_ERR_BAD_ARG, "buffer holds %zu bytes, %zu needed", bytes, need);
     CK(cudaDeviceSynchronize());
+    if (kind == SBM_LINEAR && G.nib)
+    {
+        // the caller sees one byte per response whatever the device layout
+        uint8_t *d_bytes = nullptr;
+        CK(cudaMalloc(&d_bytes, need));
+        k_unpack_nibbles<<<148 * 4, 256>>>(L.d_lm, d_bytes, need);
+        CK(cudaMemcpy(dst, d_bytes, need, cudaMemcpyDeviceToHost));
+        cudaFree(d_bytes);
+        return 0;
+    }
     CK(cudaMemcpy(dst, src, need, cudaMemcpyDeviceToHost));
     return 0;
 }
@@ -1512,8 +1551,8 @@ int sbm_similarity_map(sbm_ctx *c, int class_idx, int template_id, uint16_t *dst
     CK(cudaMemcpy(d_one, &gid, 4, cudaMemcpyHostToDevice));
     CK(cudaMemset(d_cnt, 0, 4));
     dim3 g(1, (HW + K5_TILE - 1) / K5_TILE);
-    k_similarity<<<g, K5_THREADS, 0, s.stream>>>(s.lv[c->levels - 1].d_lm, c->d_coff, c->d_tcoarse, d_one, CG.W, HW, CG.T, 1e30f, d_sink,
-                                                 d_cnt, 0, d_dump);
+    CK(launchSimilarity(CG.nib, g, s.lv[c->levels - 1].d_lm, c->d_coff, c->d_tcoarse, d_one, CG.W, HW, CG.T, 1e30f, d_sink, d_cnt, 0, d_dump,
+                        s.stream));
     CK(cudaStreamSynchronize(s.stream));
     CK(cudaMemcpy(dst, d_dump, (size_t)HW * 2, cudaMemcpyDeviceToHost));
     cudaFree(d_one), cudaFree(d_cnt), cudaFree(d_sink), cudaFree(d_dump);
@@ -1547,9 +1586,19 @@ int sbm_similarity_local(sbm_ctx *c, int class_idx, int template_id, int level, 
     CK(cudaMemcpy(d_in, &one, sizeof(Cand), cudaMemcpyHostToDevice));
     CK(cudaMemcpy(d_cnt, cnt, 8, cudaMemcpyHostToDevice));
     CK(cudaMemset(d_ev, 0, 8));
-    k_refine<<<1, K6_THREADS, 0, s.stream>>>(s.lv[level].d_lm, c->tl[level].d_tl, c->tl[level].d_feats, d_in, d_cnt, 1, d_out, d_cnt + 1, 1,
-                                             G.w, G.h, G.T, 1e30f, d_dump, 1, d_ev);
+    const uint8_t *lm = s.lv[level].d_lm;
+    uint8_t *d_bytes = nullptr;
+    if (G.nib) // the coarsest level is never refined by the pipeline; the tap unpacks it first
+    {
+        CK(cudaMalloc(&d_bytes, G.lm_alloc));
+        CK(cudaMemsetAsync(d_bytes, 0, G.lm_alloc, s.stream));
+        k_unpack_nibbles<<<148 * 4, 256, 0, s.stream>>>(lm, d_bytes, G.lm_bytes);
+        lm = d_bytes;
+    }
+    k_refine<<<1, K6_THREADS, 0, s.stream>>>(lm, c->tl[level].d_tl, c->tl[level].d_feats, d_in, d_cnt, 1, d_out, d_cnt + 1, 1, G.w, G.h, G.T, 1e30f,
+                                             d_dump, 1, d_ev);
     CK(cudaStreamSynchronize(s.stream));
+    cudaFree(d_bytes);
     CK(cudaMemcpy(dst, d_dump, 512, cudaMemcpyDeviceToHost));
     cudaFree(d_in), cudaFree(d_out), cudaFree(d_cnt), cudaFree(d_ev), cudaFree(d_dump);
     return 0;
@@ -1562,6 +1611,7 @@ int sbm_last_stats(sbm_ctx *c, uint64_t stats[8])
     memcpy(stats, c->stats, sizeof(c->stats));
     stats[0] = c->coarse_evals;
     stats[4] = (uint64_t)c->slot[0].launches;
+    stats[5] = c->levels > 0 && c->geom[c->levels - 1].nib ? 1 : 0;
     return 0;
 }
 
@@ -1603,8 +1653,8 @@ int sbm_time_similarity(sbm_ctx *c, float threshold, int iters, float *ms_per_la
     CK(cudaStreamBeginCapture(s.stream, cudaStreamCaptureModeThreadLocal));
     for (int i = 0; i < iters; ++i)
         // same launch as the pipeline's; the candidate counter keeps running, records beyond cap are dropped
-        k_similarity<<<g, K5_THREADS, 0, s.stream>>>(s.lv[L - 1].d_lm, c->d_coff, c->d_tcoarse, c->d_active, CG.W, HW, CG.T, threshold,
-                                                     s.d_buf[1], s.d_counts + 12, 0u, nullptr);
+        CK(launchSimilarity(CG.nib, g, s.lv[L - 1].d_lm, c->d_coff, c->d_tcoarse, c->d_active, CG.W, HW, CG.T, threshold, s.d_buf[1],
+                            s.d_counts + 12, 0u, nullptr, s.stream));
     CK(cudaStreamEndCapture(s.stream, &tg));
     CK(cudaGraphInstantiate(&te, tg, 0));
     CK(cudaGraphLaunch(te, s.stream));
@@ -1716,16 +1766,8 @@ int sbm_time_kernels(sbm_ctx *c, float threshold, int iters, float *ms, int n_ms
         }
         const uint8_t *nm = nullptr;
         SBM_TIME(3 * l + 1, (void)launchOrient(c->c, src, G.w, G.h, nm, l, c->w, weak_sq, LB.d_quant, st));
-        dim3 g2((G.w + K2_PW - 1) / K2_PW, (G.h + K2_PH - 1) / K2_PH);
         uint8_t *nd = nullptr;
-        if (G.T == 4)
-            SBM_TIME(3 * l + 2, (k_spread_linearize<4><<<g2, K2_THREADS, 0, st>>>(LB.d_quant, G.w, G.h, LB.d_lm, nd, nd)));
-        else if (G.T == 8)
-            SBM_TIME(3 * l + 2, (k_spread_linearize<8><<<g2, K2_THREADS, 0, st>>>(LB.d_quant, G.w, G.h, LB.d_lm, nd, nd)));
-        else if (G.T == 2)
-            SBM_TIME(3 * l + 2, (k_spread_linearize<2><<<g2, K2_THREADS, 0, st>>>(LB.d_quant, G.w, G.h, LB.d_lm, nd, nd)));
-        else
-            SBM_TIME(3 * l + 2, (k_spread_linearize<16><<<g2, K2_THREADS, 0, st>>>(LB.d_quant, G.w, G.h, LB.d_lm, nd, nd)));
+        SBM_TIME(3 * l + 2, (void)launchSpread(G, LB.d_quant, LB.d_lm, nd, nd, st));
     }
     const LevelGeom &CG = c->geom[L - 1];
     const int HW = CG.W * CG.H;
@@ -1734,8 +1776,8 @@ int sbm_time_kernels(sbm_ctx *c, float threshold, int iters, float *ms, int n_ms
     uint32_t *d_tmp = nullptr;
     CK(cudaMalloc(&d_tmp, COUNT_WORDS * 4));
     CK(cudaMemsetAsync(d_tmp, 0, COUNT_WORDS * 4, st));
-    SBM_TIME(3 * L, (k_similarity<<<gs, K5_THREADS, 0, st>>>(s.lv[L - 1].d_lm, c->d_coff, c->d_tcoarse, c->d_active, CG.W, HW, CG.T, threshold,
-                                                             s.d_buf[1], d_tmp, 0u, nullptr)));
+    SBM_TIME(3 * L, (void)launchSimilarity(CG.nib, gs, s.lv[L - 1].d_lm, c->d_coff, c->d_tcoarse, c->d_active, CG.W, HW, CG.T, threshold, s.d_buf[1],
+                                           d_tmp, 0u, nullptr, st));
     // refinement of the frame's own coarse candidates (stage counts of the last real run), output discarded
     int stage = 1;
     for (int l = L - 2; l >= 0; --l, ++stage)

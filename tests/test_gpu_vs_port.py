@@ -49,6 +49,12 @@ CONFIGS = [
     (64, 66, 3, (2,), 4, (20, 16), 16, 30.0, False),         # width not a multiple of 4: unaligned rows everywhere
     (48, 70, 1, (2,), 4, (20, 16), 16, 30.0, True),          # same, one channel, masked
     (192, 208, 3, (4, 8), 6, (60, 50), 50, 30.0, False),     # width not a multiple of the 64 / 128 pixel kernel tiles
+    # the coarsest level's memories are nibble-packed when its W is even (k_similarity_nib), byte-wide otherwise:
+    (64, 72, 1, (2,), 4, (20, 16), 16, 30.0, False),         # T = 2 on top, W = 36: packed, generic writer path
+    (96, 128, 3, (16,), 4, (40, 36), 20, 30.0, False),       # T = 16 on top, W = 8: packed, generic writer path
+    (80, 144, 1, (4, 8), 5, (36, 30), 30, 30.0, True),       # T = 8 on top, W = 9 (odd): byte-wide fallback
+    (128, 176, 3, (4, 8), 5, (40, 36), 90, 30.0, False),     # W = 11 (odd) with > 63 features: byte-wide, u16 widening
+    (128, 224, 3, (4, 8), 5, (40, 36), 90, 30.0, False),     # W = 14 (W % 8 = 6) with > 63 features: packed, ragged row ends
 ]
 
 
@@ -103,3 +109,18 @@ def test_local_patch_sums():
     for t in range(3):
         for (x, y) in ((32, 32), (100, 77), (163, 131)):
             assert np.array_equal(det.similarity_local("c", t, 0, x, y), orc.similarity_local(0, t, 0, x, y))
+
+
+def test_byte_wide_coarse_level_by_environment():
+    """SBM_COARSE_NIBBLES=0 keeps k_similarity (one byte per response) on the coarsest level for every shape: the
+    same parity tests in a fresh process, including the > 1024-offset chunks of the 8191-feature template"""
+    import os
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, SBM_COARSE_NIBBLES="0")
+    r = subprocess.run([sys.executable, "-m", "pytest", "-q", "-x", "-m", "gpu", "tests/test_gpu_vs_port.py::test_cuda_equals_port",
+                        "tests/test_gpu_edge_cases.py::test_feature_count_limit_8191", "tests/test_gpu_parity.py"],
+                       cwd=root, env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:]
