@@ -23,6 +23,9 @@ def main():
 
     from test_gpu_large import cut_templates, dense_image
 
+    import shape_based_matching_b200._capi as capi
+    if len(sys.argv) > 1:
+        capi.LIB_PATH = sys.argv[1]  # a variant build of the library
     from shape_based_matching_b200 import DEVICE_REC, Detector
 
     peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
