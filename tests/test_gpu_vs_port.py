@@ -55,6 +55,7 @@ CONFIGS = [
     (80, 144, 1, (4, 8), 5, (36, 30), 30, 30.0, True),       # T = 8 on top, W = 9 (odd): byte-wide fallback
     (128, 176, 3, (4, 8), 5, (40, 36), 90, 30.0, False),     # W = 11 (odd) with > 63 features: byte-wide, u16 widening
     (128, 224, 3, (4, 8), 5, (40, 36), 90, 30.0, False),     # W = 14 (W % 8 = 6) with > 63 features: packed, ragged row ends
+    (88, 104, 3, (4, 4), 6, (30, 26), 40, 25.0, False),      # level-0 W = 26 (W % 4 = 2): k_refine's per-row shift path
 ]
 
 
