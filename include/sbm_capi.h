@@ -178,7 +178,8 @@ int sbm_quantized_orientations(sbm_ctx *ctx, const uint8_t *img, int w, int h, i
 /* Counters of the most recent frame: [0] coarse evaluations (sum over matched templates of
  * in-image features * template_positions), [1] coarse candidates, [2] local evaluations,
  * [3] records after refinement, [4] kernels launched by the most recent call, [5] 1 when the coarsest level's
- * linear memories hold two responses per byte for the current frame shape (its W is even; k_similarity_nib). */
+ * linear memories hold two responses per byte for the current frame shape (its W is even; k_similarity_nib),
+ * [6] 1 when level 0 is stored tiled for the refinement (its W is a multiple of 16; k_refine_tiled). */
 int sbm_last_stats(sbm_ctx *ctx, uint64_t stats[8]);
 
 /* Device time of the most recent match call in milliseconds (CUDA events on the launching stream;

@@ -111,6 +111,7 @@ struct LevelGeom
     int T = 0, w = 0, h = 0, W = 0, H = 0;
     size_t lm_bytes = 0, lm_alloc = 0;
     bool nib = false; // memories packed two responses per byte (the coarsest level when W is even): k_similarity_nib reads them
+    bool tiled = false; // memories tiled 8 rows x 16 bytes per 128-byte line (refined levels with W % 16 == 0): k_refine_tiled
 };
 
 // templates of one pyramid level on the device
@@ -264,6 +265,19 @@ bool coarseNibbles()
     return on;
 }
 
+// SBM_REFINE_TILED=0 keeps the refined levels flat (k_refine) whatever their shape, =1 tiles them where the shape allows
+#ifndef SBM_REFINE_TILED_DEFAULT
+#define SBM_REFINE_TILED_DEFAULT 0
+#endif
+bool refineTiled()
+{
+    static const bool on = [] {
+        const char *e = getenv("SBM_REFINE_TILED");
+        return e ? atoi(e) != 0 : SBM_REFINE_TILED_DEFAULT;
+    }();
+    return on;
+}
+
 int ensureShape(sbm_ctx *c, int w, int h, int ch)
 {
     if (c->w == w && c->h == h && c->c == ch && !c->geom.empty())
@@ -286,6 +300,10 @@ int ensureShape(sbm_ctx *c, int w, int h, int ch)
         // (K5a runs whole warps: up to 31 lanes x 16 positions beyond the last reported one)
         G.lm_alloc = G.lm_bytes + std::max(WH, (size_t)16 * G.W + 16) + 1024;
         G.nib = l == c->levels - 1 && (G.W & 1) == 0 && coarseNibbles();
+        // K5b's levels: tiles need whole 16-byte segments per row and an orientation stride of whole tile rows
+        G.tiled = l < c->levels - 1 && (G.W & 15) == 0 && (((size_t)G.T * G.T * G.H) & 7) == 0 && refineTiled();
+        if (G.tiled) // rows up to 16 (+1 for the wrap) behind the last memory, rounded up to a tile row
+            G.lm_alloc += (size_t)24 * G.W;
     }
     c->w = w, c->h = h, c->c = ch;
     ++c->shape_gen;
@@ -296,18 +314,21 @@ int ensureShape(sbm_ctx *c, int w, int h, int ch)
 
 // K5b walks the candidate list grid-stride with a static split, so the grid is exactly the number of CTAs that are
 // resident at once (a CTA that starts after the others have finished would do its whole share alone)
-int refineGrid()
+int refineGrid(bool tiled = false)
 {
-    static int grid = 0;
+    static int grids[2] = {0, 0};
+    int &grid = grids[tiled ? 1 : 0];
     if (!grid)
     {
         int dev = 0, sms = 148, per_sm = 0;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_refine, K6_THREADS, 0) != cudaSuccess || per_sm < 1)
+        const cudaError_t e = tiled ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_refine_tiled, K6_THREADS, 0)
+                                    : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_refine, K6_THREADS, 0);
+        if (e != cudaSuccess || per_sm < 1)
             per_sm = 1;
-        if (const char *e = getenv("SBM_REFINE_CTAS_PER_SM"))
-            per_sm = std::max(1, atoi(e));
+        if (const char *ev = getenv("SBM_REFINE_CTAS_PER_SM"))
+            per_sm = std::max(1, atoi(ev));
         grid = sms * per_sm;
     }
     return grid;
@@ -574,6 +595,9 @@ int ensureActive(sbm_ctx *c, const int *class_idx, int n_classes)
 cudaError_t launchSpread(const LevelGeom &G, const uint8_t *quant, uint8_t *lm, uint8_t *dbg_spread, uint8_t *dbg_resp, cudaStream_t st);
 cudaError_t launchSimilarity(bool nib, dim3 grid, const uint8_t *lm, const uint32_t *coff, const TemplCoarse *tc, const uint32_t *active, int W,
                              int HW, int T, float threshold, Cand *out, uint32_t *counter, uint32_t cap, uint16_t *dump, cudaStream_t st);
+cudaError_t launchRefine(bool tiled, int grid, const uint8_t *lm, const TemplLevel *tl, const Feat *feats, const Cand *in, const uint32_t *in_count,
+                         uint32_t in_cap, Cand *out, uint32_t *out_count, uint32_t out_cap, int w, int h, int T, float threshold, uint16_t *dump,
+                         int raw_center, unsigned long long *local_evals, cudaStream_t st);
 
 int prepare(sbm_ctx *c, Slot &s, int w, int h, int ch, const int *class_idx, int n_classes)
 {
@@ -649,9 +673,8 @@ int enqueueFrame(sbm_ctx *c, Slot &s, const uint8_t *d_img, const uint8_t *d_mas
         out_cnt = (last && user_count) ? user_count : s.d_counts + stage;
         if (c->n_active > 0)
         {
-            k_refine<<<refineGrid(), K6_THREADS, 0, st>>>(s.lv[l].d_lm, c->tl[l].d_tl, c->tl[l].d_feats, in, in_cnt, in_cap, out, out_cnt, out_cap,
-                                                     G.w, G.h, G.T, threshold, nullptr, 0,
-                                                     reinterpret_cast<unsigned long long *>(s.d_counts + 10));
+            CK(launchRefine(G.tiled, refineGrid(G.tiled), s.lv[l].d_lm, c->tl[l].d_tl, c->tl[l].d_feats, in, in_cnt, in_cap, out, out_cnt, out_cap, G.w,
+                            G.h, G.T, threshold, nullptr, 0, reinterpret_cast<unsigned long long *>(s.d_counts + 10), st));
             ++launches;
         }
         in = out, in_cap = out_cap, in_cnt = out_cnt;
@@ -691,13 +714,28 @@ template <typename... A> int addKernel(cudaGraph_t g, cudaGraphNode_t *node, con
     return 0;
 }
 
-void *spreadFunc(int T, bool nib)
+void *spreadFunc(int T, bool nib, bool tiled)
 {
     if (nib)
         return T == 4 ? (void *)k_spread_linearize<4, true> : T == 8 ? (void *)k_spread_linearize<8, true>
                : T == 2 ? (void *)k_spread_linearize<2, true> : (void *)k_spread_linearize<16, true>;
+    if (tiled)
+        return T == 4 ? (void *)k_spread_linearize<4, false, true> : T == 8 ? (void *)k_spread_linearize<8, false, true>
+               : T == 2 ? (void *)k_spread_linearize<2, false, true> : (void *)k_spread_linearize<16, false, true>;
     return T == 4 ? (void *)k_spread_linearize<4> : T == 8 ? (void *)k_spread_linearize<8> : T == 2 ? (void *)k_spread_linearize<2>
                                                                                                      : (void *)k_spread_linearize<16>;
+}
+
+void *refineFunc(bool tiled) { return tiled ? (void *)k_refine_tiled : (void *)k_refine; }
+
+cudaError_t launchRefine(bool tiled, int grid, const uint8_t *lm, const TemplLevel *tl, const Feat *feats, const Cand *in, const uint32_t *in_count,
+                         uint32_t in_cap, Cand *out, uint32_t *out_count, uint32_t out_cap, int w, int h, int T, float threshold, uint16_t *dump,
+                         int raw_center, unsigned long long *local_evals, cudaStream_t st)
+{
+    void *argv[] = {(void *)&lm,  (void *)&tl,        (void *)&feats,   (void *)&in, (void *)&in_count, (void *)&in_cap,
+                    (void *)&out, (void *)&out_count, (void *)&out_cap, (void *)&w,  (void *)&h,        (void *)&T,
+                    (void *)&threshold, (void *)&dump, (void *)&raw_center, (void *)&local_evals};
+    return cudaLaunchKernel(refineFunc(tiled), dim3(grid), dim3(K6_THREADS), argv, 0, st);
 }
 
 void *similarityFunc(bool nib) { return nib ? (void *)k_similarity_nib : (void *)k_similarity; }
@@ -707,7 +745,7 @@ cudaError_t launchSpread(const LevelGeom &G, const uint8_t *quant, uint8_t *lm, 
     dim3 g2((G.w + K2_PW - 1) / K2_PW, (G.h + K2_PH - 1) / K2_PH);
     int w = G.w, h = G.h;
     void *argv[] = {(void *)&quant, (void *)&w, (void *)&h, (void *)&lm, (void *)&dbg_spread, (void *)&dbg_resp};
-    return cudaLaunchKernel(spreadFunc(G.T, G.nib), g2, dim3(K2_THREADS), argv, 0, st);
+    return cudaLaunchKernel(spreadFunc(G.T, G.nib, G.tiled), g2, dim3(K2_THREADS), argv, 0, st);
 }
 
 cudaError_t launchSimilarity(bool nib, dim3 grid, const uint8_t *lm, const uint32_t *coff, const TemplCoarse *tc, const uint32_t *active, int W,
@@ -779,7 +817,7 @@ int buildGraph(sbm_ctx *c, Slot &s, const uint8_t *src0, float threshold, bool w
             s.n_orient0 = n_or, s.f_orient0 = orientFunc(c->c, th), s.g_orient0 = g1;
         dim3 g2((G.w + K2_PW - 1) / K2_PW, (G.h + K2_PH - 1) / K2_PH);
         const uint8_t *qin = LB.d_quant;
-        if ((rc = addKernel(g, &n_sp, {n_or}, spreadFunc(G.T, G.nib), g2, dim3(K2_THREADS), qin, G.w, G.h, LB.d_lm, null_dbg, null_dbg)))
+        if ((rc = addKernel(g, &n_sp, {n_or}, spreadFunc(G.T, G.nib, G.tiled), g2, dim3(K2_THREADS), qin, G.w, G.h, LB.d_lm, null_dbg, null_dbg)))
             return rc;
         spread_node[l] = n_sp;
         launches += 2;
@@ -823,7 +861,7 @@ int buildGraph(sbm_ctx *c, Slot &s, const uint8_t *src0, float threshold, bool w
             int raw_center = 0;
             unsigned long long *ev = reinterpret_cast<unsigned long long *>(s.d_counts + 10);
             cudaGraphNode_t n_ref;
-            if ((rc = addKernel(g, &n_ref, {tail, spread_node[l]}, (void *)k_refine, dim3(refineGrid()), dim3(K6_THREADS), lm, tl, ff, cin, cin_cnt, in_cap,
+            if ((rc = addKernel(g, &n_ref, {tail, spread_node[l]}, refineFunc(G.tiled), dim3(refineGrid(G.tiled)), dim3(K6_THREADS), lm, tl, ff, cin, cin_cnt, in_cap,
                                 out, out_cnt, out_cap, G.w, G.h, G.T, threshold, nodump, raw_center, ev)))
                 return rc;
             tail = n_ref;
@@ -1511,6 +1549,15 @@ int sbm_get_intermediate(sbm_ctx *c, int level, int kind, void *dst, size_t byte
     if (bytes != need)
         return fail(SBM_ERR_BAD_ARG, "buffer holds %zu bytes, %zu needed", bytes, need);
     CK(cudaDeviceSynchronize());
+    if (kind == SBM_LINEAR && G.tiled)
+    {
+        uint8_t *d_bytes = nullptr;
+        CK(cudaMalloc(&d_bytes, need));
+        k_untile<<<148 * 4, 256>>>(L.d_lm, d_bytes, need, (uint32_t)G.W);
+        CK(cudaMemcpy(dst, d_bytes, need, cudaMemcpyDeviceToHost));
+        cudaFree(d_bytes);
+        return 0;
+    }
     if (kind == SBM_LINEAR && G.nib)
     {
         // the caller sees one byte per response whatever the device layout
@@ -1595,8 +1642,8 @@ int sbm_similarity_local(sbm_ctx *c, int class_idx, int template_id, int level, 
         k_unpack_nibbles<<<148 * 4, 256, 0, s.stream>>>(lm, d_bytes, G.lm_bytes);
         lm = d_bytes;
     }
-    k_refine<<<1, K6_THREADS, 0, s.stream>>>(lm, c->tl[level].d_tl, c->tl[level].d_feats, d_in, d_cnt, 1, d_out, d_cnt + 1, 1, G.w, G.h, G.T, 1e30f,
-                                             d_dump, 1, d_ev);
+    CK(launchRefine(G.tiled, 1, lm, c->tl[level].d_tl, c->tl[level].d_feats, d_in, d_cnt, 1, d_out, d_cnt + 1, 1, G.w, G.h, G.T, 1e30f, d_dump, 1,
+                    d_ev, s.stream));
     CK(cudaStreamSynchronize(s.stream));
     cudaFree(d_bytes);
     CK(cudaMemcpy(dst, d_dump, 512, cudaMemcpyDeviceToHost));
@@ -1612,6 +1659,7 @@ int sbm_last_stats(sbm_ctx *c, uint64_t stats[8])
     stats[0] = c->coarse_evals;
     stats[4] = (uint64_t)c->slot[0].launches;
     stats[5] = c->levels > 0 && c->geom[c->levels - 1].nib ? 1 : 0;
+    stats[6] = c->levels > 1 && c->geom[0].tiled ? 1 : 0;
     return 0;
 }
 
@@ -1784,9 +1832,9 @@ int sbm_time_kernels(sbm_ctx *c, float threshold, int iters, float *ms, int n_ms
     {
         const LevelGeom &G = c->geom[l];
         if (stage == 1)
-            SBM_TIME(3 * L + stage, (k_refine<<<refineGrid(), K6_THREADS, 0, st>>>(s.lv[l].d_lm, c->tl[l].d_tl, c->tl[l].d_feats, s.d_buf[0], s.d_counts + 0,
-                                                                              s.cap, s.d_buf[1], d_tmp + 1, 0u, G.w, G.h, G.T, threshold, nullptr, 0,
-                                                                              reinterpret_cast<unsigned long long *>(d_tmp + 10))));
+            SBM_TIME(3 * L + stage, (void)launchRefine(G.tiled, refineGrid(G.tiled), s.lv[l].d_lm, c->tl[l].d_tl, c->tl[l].d_feats, s.d_buf[0],
+                                                       s.d_counts + 0, s.cap, s.d_buf[1], d_tmp + 1, 0u, G.w, G.h, G.T, threshold, nullptr, 0,
+                                                       reinterpret_cast<unsigned long long *>(d_tmp + 10), st));
     }
     if (s.gexec && s.graph_epoch == c->epoch)
     {

@@ -130,12 +130,15 @@ def test_masks():
     same_list(det.match_records(img, 30.0, ["a"], masks=full), orc.match(30.0))
 
 
-def test_templates_larger_than_the_frame_and_features_outside():
+@pytest.mark.parametrize("hw", [(64, 96), (64, 128)], ids=["flat_level0", "tiled_level0"])
+def test_templates_larger_than_the_frame_and_features_outside(hw):
+    """level-0 W = 24 keeps the flat memories, W = 32 the tiled ones (k_refine_tiled): clamps that go negative, patches
+    that run over the end of a row and features outside the image must read the same bytes in both"""
     from shape_based_matching_b200 import Detector
 
     rng = np.random.default_rng(6)
     T = (4, 8)
-    img = synth_image(rng, 64, 96, 3)
+    img = synth_image(rng, hw[0], hw[1], 3)
     # template 0: bigger than the frame at both levels (template_positions <= 0); template 1: fits, but some of its
     # features lie outside the coarse image and are skipped (line2Dup.cpp:836); template 2: ordinary
     tdesc = np.array([[[400, 300, 0, 0, 20], [200, 150, 0, 0, 10]],
@@ -158,8 +161,11 @@ def test_templates_larger_than_the_frame_and_features_outside():
     for thr in (10.0, 35.0):
         same_list(det.match_candidates(img, thr, ["c"]), orc.match(thr, finalize=False))
         same_list(det.match_records(img, thr, ["c"]), orc.match(thr))
+    import os
+    if os.environ.get("SBM_REFINE_TILED", "") == "1":
+        assert det.last_stats()["refine_tiled"] == (1 if hw[1] % 64 == 0 else 0)
     for t in range(3):
-        assert np.array_equal(det.similarity_map("c", t, (4, 6)), orc.similarity(0, t)), t
+        assert np.array_equal(det.similarity_map("c", t, (hw[0] // 16, hw[1] // 16)), orc.similarity(0, t)), t
 
 
 def test_shape_changes_on_a_live_context():

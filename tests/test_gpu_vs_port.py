@@ -112,16 +112,18 @@ def test_local_patch_sums():
             assert np.array_equal(det.similarity_local("c", t, 0, x, y), orc.similarity_local(0, t, 0, x, y))
 
 
-def test_byte_wide_coarse_level_by_environment():
-    """SBM_COARSE_NIBBLES=0 keeps k_similarity (one byte per response) on the coarsest level for every shape: the
-    same parity tests in a fresh process, including the > 1024-offset chunks of the 8191-feature template"""
+def test_flat_byte_wide_layouts_by_environment():
+    """SBM_COARSE_NIBBLES=0 keeps k_similarity (one byte per response) on the coarsest level and SBM_REFINE_TILED=0
+    keeps k_refine (flat memories) on the refined levels for every shape: the same parity tests in a fresh process,
+    including the > 1024-offset chunks of the 8191-feature template"""
     import os
     import subprocess
     import sys
 
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    env = dict(os.environ, SBM_COARSE_NIBBLES="0")
+    env = dict(os.environ, SBM_COARSE_NIBBLES="0", SBM_REFINE_TILED="0")
     r = subprocess.run([sys.executable, "-m", "pytest", "-q", "-x", "-m", "gpu", "tests/test_gpu_vs_port.py::test_cuda_equals_port",
-                        "tests/test_gpu_edge_cases.py::test_feature_count_limit_8191", "tests/test_gpu_parity.py"],
+                        "tests/test_gpu_edge_cases.py::test_feature_count_limit_8191",
+                        "tests/test_gpu_edge_cases.py::test_templates_larger_than_the_frame_and_features_outside", "tests/test_gpu_parity.py"],
                        cwd=root, env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-3000:]
