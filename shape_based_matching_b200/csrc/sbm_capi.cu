@@ -267,7 +267,7 @@ bool coarseNibbles()
 
 // SBM_REFINE_TILED=0 keeps the refined levels flat (k_refine) whatever their shape, =1 tiles them where the shape allows
 #ifndef SBM_REFINE_TILED_DEFAULT
-#define SBM_REFINE_TILED_DEFAULT 0
+#define SBM_REFINE_TILED_DEFAULT 1
 #endif
 bool refineTiled()
 {

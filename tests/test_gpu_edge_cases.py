@@ -162,7 +162,7 @@ def test_templates_larger_than_the_frame_and_features_outside(hw):
         same_list(det.match_candidates(img, thr, ["c"]), orc.match(thr, finalize=False))
         same_list(det.match_records(img, thr, ["c"]), orc.match(thr))
     import os
-    if os.environ.get("SBM_REFINE_TILED", "") == "1":
+    if os.environ.get("SBM_REFINE_TILED", "1") != "0":
         assert det.last_stats()["refine_tiled"] == (1 if hw[1] % 64 == 0 else 0)
     for t in range(3):
         assert np.array_equal(det.similarity_map("c", t, (hw[0] // 16, hw[1] // 16)), orc.similarity(0, t)), t
