@@ -515,7 +515,8 @@ int ensureTemplates(sbm_ctx *c)
                                 return fail(SBM_ERR_BAD_ARG, "feature label %d out of range", f.label);
                             uint32_t a = (uint32_t)f.label * T * T * WH + (uint32_t)((f.y % T) * T + f.x % T) * WH +
                                          (uint32_t)(f.y / T) * W + (uint32_t)(f.x / T);
-                            cls[(a >> 2) & 3].push_back(a);
+                            // k_similarity_nib has two shift classes (bit 3 of the offset): buckets 1 and 3 only, half the padding
+                            cls[G.nib ? ((a >> 3) & 1) * 2 + 1 : (a >> 2) & 3].push_back(a);
                         }
                         int nv = 0, stored = 0;
                         for (int k = 0; k < 4; ++k)
