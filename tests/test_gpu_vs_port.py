@@ -56,6 +56,8 @@ CONFIGS = [
     (128, 176, 3, (4, 8), 5, (40, 36), 90, 30.0, False),     # W = 11 (odd) with > 63 features: byte-wide, u16 widening
     (128, 224, 3, (4, 8), 5, (40, 36), 90, 30.0, False),     # W = 14 (W % 8 = 6) with > 63 features: packed, ragged row ends
     (88, 104, 3, (4, 4), 6, (30, 26), 40, 25.0, False),      # level-0 W = 26 (W % 4 = 2): k_refine's per-row shift path
+    (128, 192, 3, (4, 8), 6, (40, 36), 40, 30.0, True),      # level-0 W = 48: tiled level 0 (k_refine_tiled) with a mask
+    (192, 256, 3, (8, 8), 5, (60, 50), 70, 10.0, False),     # T = 8 on both levels, level-0 W = 32: tiled writer for T = 8
 ]
 
 
