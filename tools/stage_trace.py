@@ -20,7 +20,7 @@ L = capi.lib()
 L.sbm_trace_read.argtypes = [ctypes.POINTER(ctypes.c_ulonglong), ctypes.c_int]
 buf = (ctypes.c_ulonglong * 16)()
 SIM = ("ctas", "staged (offsets + rawmin + barrier)", "gather loop done", "-", "-", "-", "-", "ctas skipped (tile beyond tp)")
-REF = ("candidates", "count+candidate+template loaded", "barrier 1", "feature bases staged + barrier", "gather loop done (warp 0)",
+REF = ("candidates", "count + candidate loaded", "barrier 1", "feature bases staged + barrier", "gather loop done (warp 0)",
        "partials barrier", "arg-max barrier", "record written")
 for thr in (99.9, 90.0, 80.0):
     det.match_records(case["img"], thr, [cid], cap=1 << 16)
