@@ -73,7 +73,7 @@ constexpr uint32_t HEAD_RECS = 1024;
 int orientTileH(int w, int h)
 {
     static const int forced = getenv("SBM_ORIENT_TH") ? atoi(getenv("SBM_ORIENT_TH")) : 0;
-    if (forced == 8 || forced == 16 || forced == 32)
+    if (forced == 8 || forced == 16 || forced == 28 || forced == 32)
         return forced;
     const int cols = (w + K1_TW - 1) / K1_TW;
     if (cols * ((h + 31) / 32) >= SBM_TALL_MIN)
@@ -84,8 +84,8 @@ int orientTileH(int w, int h)
 void *orientFunc(int ch, int th)
 {
     if (ch == 3)
-        return th == 32 ? (void *)k_orient<3, 32> : th == 16 ? (void *)k_orient<3, 16> : (void *)k_orient<3, 8>;
-    return th == 32 ? (void *)k_orient<1, 32> : th == 16 ? (void *)k_orient<1, 16> : (void *)k_orient<1, 8>;
+        return th == 32 ? (void *)k_orient<3, 32> : th == 28 ? (void *)k_orient<3, 28> : th == 16 ? (void *)k_orient<3, 16> : (void *)k_orient<3, 8>;
+    return th == 32 ? (void *)k_orient<1, 32> : th == 28 ? (void *)k_orient<1, 28> : th == 16 ? (void *)k_orient<1, 16> : (void *)k_orient<1, 8>;
 }
 
 // one K1 launch on stream st (match path: no dump outputs)

@@ -182,7 +182,9 @@ def test_shape_changes_on_a_live_context():
             same_list(g, orc.match(30.0))
 
 
-@pytest.mark.parametrize("shape,T", [((32, 32, 1), (4, 8)), ((32, 48, 3), (4, 8)), ((16, 16, 3), (4,)), ((8, 64, 1), (2, 4))])
+# the last three: 2 to 4 rows left below the last full 16-row K1 tile (its vertical pass needs 5 rows beyond the tile)
+@pytest.mark.parametrize("shape,T", [((32, 32, 1), (4, 8)), ((32, 48, 3), (4, 8)), ((16, 16, 3), (4,)), ((8, 64, 1), (2, 4)),
+                                     ((36, 64, 1), (4,)), ((34, 80, 3), (2,)), ((52, 64, 3), (4,))])
 def test_frames_smaller_than_a_kernel_tile(shape, T):
     """frames far smaller than any kernel tile: every intermediate, every raw similarity map and the (usually empty)
     lists still equal the restatement's"""
@@ -191,6 +193,7 @@ def test_frames_smaller_than_a_kernel_tile(shape, T):
     rng = np.random.default_rng(sum(shape) + len(T))
     img = (rng.integers(0, 256, shape, dtype=np.uint8) // 4).astype(np.uint8)
     img[shape[0] // 4 : shape[0] // 2 + 2, shape[1] // 3 : shape[1] // 3 * 2] = 230  # one bright block: strong edges
+    img[-5:, : shape[1] // 2] = 200  # and an edge in the last rows of the frame
     tdesc, feats = synth_templates(rng, 4, len(T), (10, 6), 8)
     det = Detector(8, T, 30.0, 60.0)
     det.setClassTemplates("s", tdesc, feats)
