@@ -69,7 +69,7 @@ constexpr int COUNT_WORDS = 16; // [0..levels-1] stage counts, [10..11] u64 loca
 constexpr uint32_t HEAD_RECS = 1024;
 
 // K1 tile height for a w x h level: 64x32 tiles unless that leaves the GPU under two CTAs per SM, then 64x16.
-// SBM_ORIENT_TH=8|16|32 forces one height (experiments).
+// SBM_ORIENT_TH=8|16|28|32 forces one height (experiments).
 int orientTileH(int w, int h)
 {
     static const int forced = getenv("SBM_ORIENT_TH") ? atoi(getenv("SBM_ORIENT_TH")) : 0;
@@ -78,6 +78,8 @@ int orientTileH(int w, int h)
     const int cols = (w + K1_TW - 1) / K1_TW;
     if (cols * ((h + 31) / 32) >= SBM_TALL_MIN)
         return 32;
+    // 64x28 tiles fill the 148 SMs evenly at 1024 rows (592 CTAs = 4 per SM; the kernel alone 13.6 -> 12.5 us) but the
+    // frame as a whole got no faster (graph 52.2 -> 52.8 us, 23.2 -> 23.5 us per frame in flight): not used
     return 16; // 64x8 tiles (512 CTAs at level 1 of a 1024^2 frame) measured no faster than 64x16: 8.5 vs 8.1 us
 }
 
