@@ -43,8 +43,9 @@ N_TEMPLATES = 360
 REC_CAP = 512  # per-frame record capacity of the device-resident path = the all_gather payload (20 B each); M1 frames
 # produce ~100 records; the counts are checked after the timed region, an overflow aborts the run
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE k_similarity launch on this workload, from the committed
-# `ncu --set full` capture (profiles/r1z_summary.md); bench.py itself never runs under a profiler
-K_SIMILARITY_DRAM_BYTES = {"k_similarity": 2288384, "k_similarity_nib": 1247232}
+# `ncu --set full` capture (profiles/r1z_summary.md for the byte kernel, profiles/r1final_summary.md for the
+# nibble kernel); bench.py itself never runs under a profiler
+K_SIMILARITY_DRAM_BYTES = {"k_similarity": 2288384, "k_similarity_nib": 1231872}
 
 
 def load_workload():
@@ -428,7 +429,7 @@ def main():
     roofline = {
         "kernel": "k_similarity_nib" if nib else "k_similarity", "bound": "hbm", "achieved": sim_gbs, "peak": hbm_peak, "unit": "GB/s",
         "frac": sim_gbs / hbm_peak, "traffic": K_SIMILARITY_DRAM_BYTES["k_similarity_nib" if nib else "k_similarity"],
-        "traffic_source": "profiles/r1z_summary.md (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum, one launch)",
+        "traffic_source": "profiles/r1final_summary.md / r1z_summary.md (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum, one launch)",
         "peak_source": peak_src,
         "algorithmic_bytes_per_launch": coarse, "avg_launch_ms": sim_ms,
         "bytes_loaded_per_evaluation": 0.5 if nib else 1.0,
