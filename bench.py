@@ -45,6 +45,7 @@ REC_CAP = 512  # per-frame record capacity of the device-resident path = the all
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE k_similarity launch on this workload, from the committed
 # `ncu --set full` capture (profiles/r1z_summary.md for the byte kernel, profiles/r1final_summary.md for the
 # nibble kernel); bench.py itself never runs under a profiler
+_JSON_FD = None  # the original stdout when fd 1 has been pointed at stderr (N > 1)
 K_SIMILARITY_DRAM_BYTES = {"k_similarity": 2288384, "k_similarity_nib": 1231872}
 
 
@@ -216,6 +217,12 @@ def main():
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
+        # NCCL prints its version banner (NCCL_DEBUG=VERSION/INFO on the box) with the C library on fd 1: point fd 1 at
+        # stderr while the process group lives, so that stdout carries the one JSON line and nothing else
+        global _JSON_FD
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=dev)
 
     base, cid, tdesc, feats, nf = load_workload()
@@ -491,7 +498,11 @@ def main():
     }
     if tshard:
         line["template_sharded"] = tshard
-    print(json.dumps(line), flush=True)
+    if _JSON_FD is not None:
+        sys.stdout.flush()
+        os.write(_JSON_FD, (json.dumps(line) + "\n").encode())
+    else:
+        print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
 
