@@ -113,32 +113,44 @@ class RefDetector:
             self.h, class_id.encode(), zero_id, C.c_float(theta), C.c_float(cx), C.c_float(cy)
         )
 
-    def match(self, img, threshold, class_ids=(), omp_threads=1, cap=1 << 20):
+    @staticmethod
+    def _mask_arg(img, mask):
+        """NULL, or the u8 [h][w] mask Detector::match takes as `masks` (line2Dup.cpp:1078-1086)"""
+        if mask is None:
+            return None, None
+        mask = np.ascontiguousarray(mask, dtype=np.uint8)
+        assert mask.shape == img.shape[:2], "mask.size() != source.size()"
+        return mask, mask.ctypes.data_as(C.c_void_p)
+
+    def match(self, img, threshold, class_ids=(), omp_threads=1, cap=1 << 20, mask=None):
         img, a = _img_args(img)
+        _keep, m = self._mask_arg(img, mask)
         out = np.zeros(cap, MATCH_DTYPE)
         n = C.c_int()
         self._chk(
             self.L.ref_match(
-                self.h, *a, C.c_float(threshold), ",".join(class_ids).encode(), omp_threads,
+                self.h, *a, m, C.c_float(threshold), ",".join(class_ids).encode(), omp_threads,
                 out.ctypes.data_as(C.c_void_p), cap, C.byref(n),
             )
         )
         return out[: n.value].copy()
 
-    def candidates(self, img, threshold, class_ids=(), cap=1 << 20):
+    def candidates(self, img, threshold, class_ids=(), cap=1 << 20, mask=None):
         img, a = _img_args(img)
+        _keep, m = self._mask_arg(img, mask)
         out = np.zeros(cap, MATCH_DTYPE)
         n = C.c_int()
         self._chk(
             self.L.ref_candidates(
-                self.h, *a, C.c_float(threshold), ",".join(class_ids).encode(), out.ctypes.data_as(C.c_void_p), cap, C.byref(n)
+                self.h, *a, m, C.c_float(threshold), ",".join(class_ids).encode(), out.ctypes.data_as(C.c_void_p), cap, C.byref(n)
             )
         )
         return out[: n.value].copy()
 
-    def front(self, img, level):
+    def front(self, img, level, mask=None):
         """-> dict(quantized, spread, response[8], linmem[8, T*T, W*H]) of one pyramid level."""
         img, a = _img_args(img)
+        _keep, m = self._mask_arg(img, mask)
         h, w = img.shape[0] >> level, img.shape[1] >> level
         T = self.T[level]
         q = np.zeros((h, w), np.uint8)
@@ -147,27 +159,29 @@ class RefDetector:
         lm = np.zeros((8, T * T, (h // T) * (w // T)), np.uint8)
         self._chk(
             self.L.ref_front(
-                self.h, *a, level, q.ctypes.data_as(C.c_void_p), s.ctypes.data_as(C.c_void_p),
+                self.h, *a, m, level, q.ctypes.data_as(C.c_void_p), s.ctypes.data_as(C.c_void_p),
                 r.ctypes.data_as(C.c_void_p), lm.ctypes.data_as(C.c_void_p),
             )
         )
         return dict(quantized=q, spread=s, response=r, linmem=lm)
 
-    def similarity(self, img, class_id, template_id):
+    def similarity(self, img, class_id, template_id, mask=None):
         img, a = _img_args(img)
+        _keep, m = self._mask_arg(img, mask)
         lv = len(self.T) - 1
         T = self.T[lv]
         H, W = (img.shape[0] >> lv) // T, (img.shape[1] >> lv) // T
         out = np.zeros((H, W), np.uint16)
-        self._chk(self.L.ref_similarity(self.h, *a, class_id.encode(), template_id, out.ctypes.data_as(C.c_void_p)))
+        self._chk(self.L.ref_similarity(self.h, *a, m, class_id.encode(), template_id, out.ctypes.data_as(C.c_void_p)))
         return out
 
-    def similarity_local(self, img, class_id, template_id, level, x, y):
+    def similarity_local(self, img, class_id, template_id, level, x, y, mask=None):
         img, a = _img_args(img)
+        _keep, m = self._mask_arg(img, mask)
         out = np.zeros((16, 16), np.uint16)
         self._chk(
             self.L.ref_similarity_local(
-                self.h, *a, class_id.encode(), template_id, level, x, y, out.ctypes.data_as(C.c_void_p)
+                self.h, *a, m, class_id.encode(), template_id, level, x, y, out.ctypes.data_as(C.c_void_p)
             )
         )
         return out
@@ -191,3 +205,33 @@ class RefDetector:
         self._chk(self.L.ref_eval_counts(self.h, *a, C.c_float(threshold), ",".join(class_ids).encode(),
                                          C.byref(ce), C.byref(cc), C.byref(le)))
         return ce.value, cc.value, le.value
+
+
+def shape_infos(angle_range, scale_range, angle_step=15.0, scale_step=0.5, cap=1 << 16):
+    """shapeInfo_producer::produce_infos of the reference (line2Dup.h:407-449) -> float32 [n, 2] = (angle, scale)"""
+    L = lib()
+    a = np.ascontiguousarray(angle_range, np.float32)
+    s = np.ascontiguousarray(scale_range, np.float32)
+    out = np.zeros((cap, 2), np.float32)
+    n = C.c_int()
+    rc = L.ref_shape_infos(a.ctypes.data_as(C.c_void_p), len(a), s.ctypes.data_as(C.c_void_p), len(s), C.c_float(angle_step),
+                           C.c_float(scale_step), out.ctypes.data_as(C.c_void_p), cap, C.byref(n))
+    if rc < 0:
+        raise RuntimeError(L.ref_last_error().decode())
+    assert n.value <= cap
+    return out[: n.value].copy()
+
+
+def shape_transform(img, angle, scale, as_mask=False):
+    """shapeInfo_producer::src_of / mask_of of the reference (line2Dup.h:379-405, :451-457)"""
+    L = lib()
+    img, a = _img_args(img)
+    ow, oh = C.c_int(), C.c_int()
+    rc = L.ref_shape_transform(*a, C.c_float(angle), C.c_float(scale), int(as_mask), None, C.byref(ow), C.byref(oh))
+    if rc < 0:
+        raise RuntimeError(L.ref_last_error().decode())
+    out = np.zeros((oh.value, ow.value, img.shape[2]), np.uint8)
+    rc = L.ref_shape_transform(*a, C.c_float(angle), C.c_float(scale), int(as_mask), out.ctypes.data_as(C.c_void_p), C.byref(ow), C.byref(oh))
+    if rc < 0:
+        raise RuntimeError(L.ref_last_error().decode())
+    return out[:, :, 0] if out.shape[2] == 1 else out

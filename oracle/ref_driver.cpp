@@ -247,29 +247,61 @@ int ref_add_template_rotate(void *h, const char *class_id, int zero_id, float th
     REF_CATCH
 }
 
+// shape_based_matching::shapeInfo_producer (line2Dup.h:344-460): the `infos` sequence of produce_infos (float
+// accumulation of `angle += angle_step` included) and src_of / mask_of of one Info.
+int ref_shape_infos(const float *angle_range, int n_angle, const float *scale_range, int n_scale, float angle_step, float scale_step,
+                    float *out, int cap, int *n_out)
+{
+    REF_TRY
+    shape_based_matching::shapeInfo_producer sp(cv::Mat(8, 8, CV_8UC1));
+    sp.angle_range.assign(angle_range, angle_range + n_angle);
+    sp.scale_range.assign(scale_range, scale_range + n_scale);
+    sp.angle_step = angle_step;
+    sp.scale_step = scale_step;
+    sp.produce_infos();
+    *n_out = (int)sp.infos.size();
+    for (int i = 0; i < (int)sp.infos.size() && i < cap; ++i)
+        out[2 * i] = sp.infos[i].angle, out[2 * i + 1] = sp.infos[i].scale;
+    return 0;
+    REF_CATCH
+}
+int ref_shape_transform(const uint8_t *img, int w, int hh, int c, float angle, float scale, int as_mask, uint8_t *out, int *ow, int *oh)
+{
+    REF_TRY
+    shape_based_matching::shapeInfo_producer sp(wrap(img, w, hh, c), as_mask ? wrap(img, w, hh, c) : cv::Mat());
+    shape_based_matching::shapeInfo_producer::Info info(angle, scale);
+    cv::Mat d = as_mask ? sp.mask_of(info) : sp.src_of(info);
+    *ow = d.cols, *oh = d.rows;
+    if (out)
+        memcpy(out, d.data, (size_t)d.cols * d.rows * d.channels());
+    return 0;
+    REF_CATCH
+}
+
 // Detector::match verbatim (line2Dup.cpp:1078-1150).  omp_threads<=0 keeps the OpenMP default.
-int ref_match(void *h, const uint8_t *img, int w, int hh, int c, float thr, const char *class_csv, int omp_threads,
+int ref_match(void *h, const uint8_t *img, int w, int hh, int c, const uint8_t *mask, float thr, const char *class_csv, int omp_threads,
               RefMatch *out, int cap, int *n_out)
 {
     REF_TRY
     if (omp_threads > 0)
         omp_set_num_threads(omp_threads);
     Probe *p = (Probe *)h;
-    std::vector<Match> m = p->match(wrap(img, w, hh, c), thr, splitIds(class_csv));
+    // mask: NULL or u8 [hh][w], handed to Detector::match as its `masks` argument (line2Dup.cpp:1078-1086)
+    std::vector<Match> m = p->match(wrap(img, w, hh, c), thr, splitIds(class_csv), mask ? wrap(mask, w, hh, 1) : cv::Mat());
     exportMatches(p, m, out, cap, n_out);
     return 0;
     REF_CATCH
 }
 
 // Candidate list BEFORE sort/unique, in the reference's serial append order (1 OpenMP thread).
-int ref_candidates(void *h, const uint8_t *img, int w, int hh, int c, float thr, const char *class_csv, RefMatch *out,
+int ref_candidates(void *h, const uint8_t *img, int w, int hh, int c, const uint8_t *mask, float thr, const char *class_csv, RefMatch *out,
                    int cap, int *n_out)
 {
     REF_TRY
     omp_set_num_threads(1);
     Probe *p = (Probe *)h;
     Probe::Front f;
-    p->front(wrap(img, w, hh, c), cv::Mat(), f, false);
+    p->front(wrap(img, w, hh, c), mask ? wrap(mask, w, hh, 1) : cv::Mat(), f, false);
     std::vector<Match> m;
     p->candidates(f, thr, splitIds(class_csv), m);
     exportMatches(p, m, out, cap, n_out);
@@ -280,13 +312,13 @@ int ref_candidates(void *h, const uint8_t *img, int w, int hh, int c, float thr,
 // Intermediates of one pyramid level.  Any output pointer may be NULL.
 //   quantized/spread: h_l*w_l bytes; response: 8*h_l*w_l; linmem: 8 * T*T * (w_l/T*h_l/T) bytes
 //   ordered [label][grid row][cell] exactly as the reference's 8 Mats laid end to end.
-int ref_front(void *h, const uint8_t *img, int w, int hh, int c, int level, uint8_t *quantized, uint8_t *spread_out,
+int ref_front(void *h, const uint8_t *img, int w, int hh, int c, const uint8_t *mask, int level, uint8_t *quantized, uint8_t *spread_out,
               uint8_t *response, uint8_t *linmem)
 {
     REF_TRY
     Probe *p = (Probe *)h;
     Probe::Front f;
-    p->front(wrap(img, w, hh, c), cv::Mat(), f, true);
+    p->front(wrap(img, w, hh, c), mask ? wrap(mask, w, hh, 1) : cv::Mat(), f, true);
     const cv::Mat &q = f.quantized[level];
     size_t n = (size_t)q.rows * q.cols;
     if (quantized)
@@ -306,12 +338,12 @@ int ref_front(void *h, const uint8_t *img, int w, int hh, int c, int level, uint
 
 // Raw coarse similarity map (u16, H*W at the last level) of one template, through the same
 // similarity_64 / similarity dispatch as matchClass (line2Dup.cpp:1189-1196).
-int ref_similarity(void *h, const uint8_t *img, int w, int hh, int c, const char *class_id, int template_id, uint16_t *out)
+int ref_similarity(void *h, const uint8_t *img, int w, int hh, int c, const uint8_t *mask, const char *class_id, int template_id, uint16_t *out)
 {
     REF_TRY
     Probe *p = (Probe *)h;
     Probe::Front f;
-    p->front(wrap(img, w, hh, c), cv::Mat(), f, false);
+    p->front(wrap(img, w, hh, c), mask ? wrap(mask, w, hh, 1) : cv::Mat(), f, false);
     const Template &t = p->getTemplates(class_id, template_id).back();
     int T = p->Ts().back();
     cv::Mat sim;
@@ -328,13 +360,13 @@ int ref_similarity(void *h, const uint8_t *img, int w, int hh, int c, const char
 }
 
 // 16x16 local similarity patch at level `level` around centre (x,y) (line2Dup.cpp:1254-1261).
-int ref_similarity_local(void *h, const uint8_t *img, int w, int hh, int c, const char *class_id, int template_id,
+int ref_similarity_local(void *h, const uint8_t *img, int w, int hh, int c, const uint8_t *mask, const char *class_id, int template_id,
                          int level, int x, int y, uint16_t *out)
 {
     REF_TRY
     Probe *p = (Probe *)h;
     Probe::Front f;
-    p->front(wrap(img, w, hh, c), cv::Mat(), f, false);
+    p->front(wrap(img, w, hh, c), mask ? wrap(mask, w, hh, 1) : cv::Mat(), f, false);
     const Template &t = p->getTemplates(class_id, template_id)[level];
     int T = p->Ts()[level];
     cv::Mat sim;

@@ -82,3 +82,16 @@ def parse_driver_templates(text):
     levels = 1 + max(k[1] for k in rows)
     tdesc = np.array([[rows[(t, l)] for l in range(levels)] for t in range(n)], np.int32)
     return tdesc, np.array(feats, np.int32).reshape(-1, 3)
+
+
+def load_masked_two_class():
+    """tests/golden/masked_two_class.npz (make_fixtures.py: make_masked_two_class) -> dict with img, mask and the two classes
+    as [(class_id, tdesc, feats)]: "circle" = all case0 templates, "a_ring" = the first `ring_templates` of them"""
+    z = dict(np.load(os.path.join(GOLDEN, "masked_two_class.npz")))
+    z["img"] = decode_png(z.pop("img_png"))
+    z["mask"] = decode_png(z.pop("mask_png"))
+    cid, tdesc, feats, nf = load_templates("case0")
+    n2 = int(z["ring_templates"])
+    z["classes"] = [("circle", tdesc, feats), ("a_ring", tdesc[:n2], feats[: int(tdesc[:n2, :, 4].sum())])]
+    z["requests"] = (("all", []), ("circle", ["circle"]), ("ring_circle", ["a_ring", "circle"]), ("circle_ring", ["circle", "a_ring"]))
+    return z

@@ -218,8 +218,48 @@ def synth_m1(seed=1234):
     return frame
 
 
+def make_masked_two_class():
+    """masked_two_class.npz: Detector::match with a mask (line2Dup.cpp:1078-1086, :439, :446-450) and with two classes in
+    the caller's order (:1124-1140), both through the reference's own code.  Frame: test/case0/2.jpg (640x480); classes
+    "circle" (the 89 case0 templates) and "a_ring" (case0 templates 0..59 under a name that sorts first, so the class
+    slots (std::map order) differ from the insertion order and both classes report the same places)."""
+    td0, ft0 = export_templates("case0", "circle", REF + "case0/%s_templ.yaml", 150)
+    n2 = 60
+    td2, ft2 = td0[:n2], ft0[: td0[:n2, :, 4].sum()]
+    img = crop_to(cv2.imread(REF + "case0/2.jpg"), 32)
+    h, w = img.shape[:2]
+    mask = np.full((h, w), 255, np.uint8)
+    mask[:, : w // 3] = 0          # a third of the frame removed
+    mask[h // 2 :, ::5] = 0        # and a comb over the lower half (any non-zero value keeps a pixel)
+    mask[5:40, w // 2 : w // 2 + 60] = 3
+    det = RefDetector(150, (4, 8))
+    det.add_class("circle", td0, ft0)
+    det.add_class("a_ring", td2, ft2)
+    d = dict(img_png=png(img), shape=np.int32(img.shape), mask_png=png(mask), T=np.int32([4, 8]), weak=np.float32(30),
+             strong=np.float32(60), num_features=np.int32(150), ring_templates=np.int32(n2))
+    thr = 70.0
+    d["threshold"] = np.float32(thr)
+    for tag, ids in (("all", []), ("circle", ["circle"]), ("ring_circle", ["a_ring", "circle"]), ("circle_ring", ["circle", "a_ring"])):
+        d["matches_" + tag] = det.match(img, thr, ids, omp_threads=1)
+        d["candidates_" + tag] = det.candidates(img, thr, ids)
+        d["masked_matches_" + tag] = det.match(img, thr, ids, omp_threads=1, mask=mask)
+        d["masked_candidates_" + tag] = det.candidates(img, thr, ids, mask=mask)
+        print("masked_two_class[%s]: %d final (%d pre-unique); masked %d (%d)" % (
+            tag, len(d["matches_" + tag]), len(d["candidates_" + tag]), len(d["masked_matches_" + tag]), len(d["masked_candidates_" + tag])))
+    assert set(d["matches_all"]["class_idx"]) == {0, 1} and set(d["masked_matches_all"]["class_idx"]) == {0, 1}
+    for l in range(2):
+        f = det.front(img, l, mask=mask)
+        d["masked_quantized%d" % l] = f["quantized"]
+        d["masked_linmem%d_sha" % l] = np.array(sha(f["linmem"]))
+    d["masked_sim_ring7"] = det.similarity(img, "a_ring", 7, mask=mask)
+    np.savez_compressed(os.path.join(HERE, "masked_two_class.npz"), **d)
+
+
 def main():
     os.makedirs(HERE, exist_ok=True)
+    if "--masked-two-class" in sys.argv:  # only this fixture (the others are unchanged)
+        make_masked_two_class()
+        return
     make_cv_pins()
 
     # ---- case1: test.cpp angle_test (test.cpp:262-420) ----
@@ -245,6 +285,7 @@ def main():
     n = 360
     nf = td1[:n, :, 4].sum()
     make_case("m1", synth_m1(), "case1[:360]", "test", td1[:n], ft1[:nf], 128, [0, 37, 74, 111, 148])
+    make_masked_two_class()
 
 
 if __name__ == "__main__":

@@ -1,11 +1,14 @@
 """Edge cases of Detector::match on the GPU: the reference's asserts and limits (line2Dup.cpp:639, :751-752, :811,
 :1195), unknown and multiple classes (:1124-1138), empty inputs, masks that remove everything, templates larger
 than the frame (template_positions <= 0, :825), capacity growth, and shape changes on a live context.  Expectations
-come from the CPU restatement (oracle/sbm_oracle.cpp) wherever there is something to compare."""
+come from tests/_refcheck.py: the reference's own code (oracle/_ref) wherever the reference accepts the input (masks,
+several classes, 8191 features, capacity growth, shape changes), the C++ restatement otherwise (frames smaller than
+the refinement window and templates larger than the frame index out of bounds in the reference)."""
 import numpy as np
 import pytest
 
-from oracle import port
+from _refcheck import Expected
+from oracle import ref
 from test_gpu_vs_port import synth_image, synth_templates
 
 pytestmark = pytest.mark.gpu
@@ -25,8 +28,7 @@ def make(rng, h=128, w=160, c=3, T=(4, 8), n=8, box=(40, 36), nf=24):
     tdesc, feats = synth_templates(rng, n, len(T), box, nf)
     det = Detector(nf, T, 30.0, 60.0)
     det.setClassTemplates("a", tdesc, feats)
-    orc = port.PortDetector(T, 30.0)
-    orc.add_class(tdesc, feats)
+    orc = Expected(T, 30.0, [("a", tdesc, feats)], num_features=nf)
     return det, orc, img, tdesc, feats
 
 
@@ -58,11 +60,10 @@ def test_feature_count_limit_8191():
         det = Detector(nf, (4,), 30.0, 60.0)
         det.setClassTemplates("big", tdesc, feats)
         if ok:
-            orc = port.PortDetector((4,), 30.0)
-            orc.add_class(tdesc, feats)
-            orc.process(img)
+            orc = Expected((4,), 30.0, [("big", tdesc, feats)], num_features=nf).process(img)
+            assert orc.pinned or not ref.available()
             same_list(det.match_records(img, 20.0, ["big"]), orc.match(20.0))
-            assert np.array_equal(det.similarity_map("big", 0, (64, 64)), orc.similarity(0, 0))
+            assert np.array_equal(det.similarity_map("big", 0, (64, 64)), orc.similarity("big", 0))
         else:
             with pytest.raises(SbmError) as e:  # CV_Error "feature size too large" (line2Dup.cpp:1195)
                 det.match_records(img, 20.0, ["big"])
@@ -81,20 +82,22 @@ def test_unknown_empty_and_multiple_classes():
     assert len(det.match_records(img, 30.0)) == 0  # no templates at all
     det.setClassTemplates("b_second", tb, fb)
     det.setClassTemplates("a_first", ta, fa)
-    orc = port.PortDetector(T, 30.0)
-    orc.add_class(ta, fa)  # class slots follow std::map order: "a_first" < "b_second"
-    orc.add_class(tb, fb)
-    orc.process(img)
+    orc = Expected(T, 30.0, [("a_first", ta, fa), ("b_second", tb, fb)], num_features=30).process(img)  # slots follow std::map order
+    assert orc.pinned or not ref.available()
     both = det.match_records(img, 30.0)  # empty list = all classes in map order (line2Dup.cpp:1124-1130)
-    same_list(both, orc.match(30.0, class_idx=(0, 1)))
+    same_list(both, orc.match(30.0))
     assert set(both["class_idx"]) == {0, 1}
     assert len(det.match_records(img, 30.0, ["nope"])) == 0  # unknown ids are skipped (:1136-1138)
     only_b = det.match_records(img, 30.0, ["nope", "b_second"])
-    want_b = orc.match(30.0, class_idx=(1,))
+    want_b = orc.match(30.0, ["nope", "b_second"])
     assert len(only_b) == len(want_b) and np.array_equal(only_b["x"], want_b["x"]) and np.array_equal(only_b["template_id"], want_b["template_id"])
     assert [m.class_id for m in det.match(img, 30.0, ["b_second"])][:1] in ([], ["b_second"])
     # caller's order matters for the candidate order: b before a
-    same_list(det.match_candidates(img, 30.0, ["b_second", "a_first"]), orc.match(30.0, class_idx=(1, 0), finalize=False))
+    same_list(det.match_candidates(img, 30.0, ["b_second", "a_first"]), orc.match(30.0, ["b_second", "a_first"], finalize=False))
+    same_list(det.match_records(img, 30.0, ["b_second", "a_first"]), orc.match(30.0, ["b_second", "a_first"]))
+    # a class named twice is matched twice (the reference appends per requested id, :1134-1139)
+    same_list(det.match_candidates(img, 30.0, ["a_first", "a_first"]), orc.match(30.0, ["a_first", "a_first"], finalize=False))
+    same_list(det.match_records(img, 30.0, ["a_first", "a_first"]), orc.match(30.0, ["a_first", "a_first"]))
     # removing a class
     det.setClassTemplates("a_first", ta[:0], fa[:0])
     assert set(det.match_records(img, 30.0)["class_idx"]) <= {0, 1}
@@ -118,6 +121,7 @@ def test_masks():
     h, w = img.shape[:2]
     zero = np.zeros((h, w), np.uint8)
     orc.process(img, zero)
+    assert orc.pinned or not ref.available()
     assert len(orc.match(5.0)) == 0
     assert len(det.match_records(img, 5.0, ["a"], masks=zero)) == 0
     assert not det.intermediate(0, 0).any()
@@ -155,9 +159,8 @@ def test_templates_larger_than_the_frame_and_features_outside(hw):
     feats = np.concatenate(feats).astype(np.int32)
     det = Detector(20, T, 30.0, 60.0)
     det.setClassTemplates("c", tdesc, feats)
-    orc = port.PortDetector(T, 30.0)
-    orc.add_class(tdesc, feats)
-    orc.process(img)
+    orc = Expected(T, 30.0, [("c", tdesc, feats)], num_features=20).process(img)
+    assert not orc.pinned  # template 0 is larger than the frame: the reference's clamp indexes before its memories
     for thr in (10.0, 35.0):
         same_list(det.match_candidates(img, thr, ["c"]), orc.match(thr, finalize=False))
         same_list(det.match_records(img, thr, ["c"]), orc.match(thr))
@@ -165,7 +168,7 @@ def test_templates_larger_than_the_frame_and_features_outside(hw):
     if os.environ.get("SBM_REFINE_TILED", "1") != "0":
         assert det.last_stats()["refine_tiled"] == (1 if hw[1] % 64 == 0 else 0)
     for t in range(3):
-        assert np.array_equal(det.similarity_map("c", t, (hw[0] // 16, hw[1] // 16)), orc.similarity(0, t)), t
+        assert np.array_equal(det.similarity_map("c", t, (hw[0] // 16, hw[1] // 16)), orc.similarity("c", t)), t
 
 
 def test_shape_changes_on_a_live_context():
@@ -198,16 +201,14 @@ def test_frames_smaller_than_a_kernel_tile(shape, T):
     det = Detector(8, T, 30.0, 60.0)
     det.setClassTemplates("s", tdesc, feats)
     det.set_debug(True)
-    orc = port.PortDetector(T, 30.0)
-    orc.add_class(tdesc, feats)
-    orc.process(img)
+    orc = Expected(T, 30.0, [("s", tdesc, feats)], num_features=8).process(img)
     for thr in (1.0, 30.0):
         same_list(det.match_candidates(img, thr, ["s"]), orc.match(thr, finalize=False))
         same_list(det.match_records(img, thr, ["s"]), orc.match(thr))
     for l in range(len(T)):
         for kind in range(4):
-            assert np.array_equal(det.intermediate(l, kind), orc.get(l, kind)), (l, kind)
+            assert np.array_equal(det.intermediate(l, kind), orc.intermediate(l, kind)), (l, kind)
     lv = len(T) - 1
     hw = ((shape[0] >> lv) // T[lv], (shape[1] >> lv) // T[lv])
     for t in range(4):
-        assert np.array_equal(det.similarity_map("s", t, hw), orc.similarity(0, t)), t
+        assert np.array_equal(det.similarity_map("s", t, hw), orc.similarity("s", t)), t

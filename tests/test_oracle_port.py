@@ -50,3 +50,30 @@ def test_port_gray_frame():
     for l in range(2):
         assert np.array_equal(det.get(l, 0).reshape(case["gray_quantized%d" % l].shape), case["gray_quantized%d" % l])
     same_list(det.match(float(case["threshold"])), case["gray_matches"])
+
+
+def test_port_masked_and_two_classes():
+    """the restatement against the reference's own outputs with a mask and with two classes in three request orders"""
+    from _fixtures import load_masked_two_class
+
+    z = load_masked_two_class()
+    det = port.PortDetector([int(t) for t in z["T"]], float(z["weak"]))
+    ids = sorted(c[0] for c in z["classes"])
+    for cid in ids:  # class slots follow std::map order
+        td, ft = next((c[1], c[2]) for c in z["classes"] if c[0] == cid)
+        det.add_class(td, ft)
+    thr = float(z["threshold"])
+    for masked in (False, True):
+        det.process(z["img"], z["mask"] if masked else None)
+        pre = "masked_" if masked else ""
+        for tag, req in z["requests"]:
+            idx = tuple(ids.index(c) for c in req) if req else tuple(range(len(ids)))
+            for kind, fin in (("candidates_", False), ("matches_", True)):
+                got, want = det.match(thr, class_idx=idx, finalize=fin), z[pre + kind + tag]
+                same_list(got, want)
+                assert np.array_equal(got["class_idx"], want["class_idx"])
+        if masked:
+            for l in range(2):
+                assert np.array_equal(det.get(l, 0).reshape(z["masked_quantized%d" % l].shape), z["masked_quantized%d" % l])
+                assert sha(det.get(l, 3)) == str(z["masked_linmem%d_sha" % l])
+            assert np.array_equal(det.similarity(ids.index("a_ring"), 7), z["masked_sim_ring7"])
