@@ -25,13 +25,14 @@
 #endif
 
 #include <cassert>
+#include <cfloat>
 #include <cmath>
 #include <map>
 #include <memory>
 #include <string>
 #include <vector>
 
-#define ANGLE_TOLERANCE 1e-3
+#define ANGLE_TOLERANCE FLT_EPSILON // line2Dup.h:8
 
 struct sbm_ctx; // include/sbm_capi.h
 
@@ -118,7 +119,7 @@ public:
                                         size_t num_features, float distance);
 
 private:
-    cv::Mat src0; // level-0 source: the GPU walks the pyrDown chain from it
+    void updateFrom(int pyrdown_steps); // update() of `src` taken through that many cv::pyrDown steps on the device
 };
 inline ColorGradientPyramid::Candidate::Candidate(int x, int y, int label, float _score) : f(x, y, label), score(_score) {}
 
@@ -230,6 +231,23 @@ public:
     /// CUDA device ordinal used by this detector (default 0; set before the first match/addTemplate).
     void setDevice(int device);
 
+    /// Multi-GPU (sbm_group_* in include/sbm_capi.h): this detector becomes rank `rank` of `n_ranks`
+    /// detectors, one per GPU of a box (one process or thread each), joined by one NCCL communicator.  Rank 0 calls
+    /// groupUniqueId() and hands the 128 bytes to the others (file, pipe, MPI ...); every rank then calls setGroup
+    /// (collective).  GROUP_TEMPLATES[_CONTIGUOUS]: the template loop of matchClass (line2Dup.cpp:1166-1170) is spread
+    /// over the GPUs -- every rank keeps all its addTemplate / readClasses calls and passes the same frame, match()
+    /// returns the unsharded list on every rank.  GROUP_FRAMES: the caller's frame loop (test_jabil.cpp:314-374) is
+    /// spread -- matchBatch() takes this rank's frames and returns the lists of all ranks' frames, rank-major.
+    enum GroupMode
+    {
+        GROUP_TEMPLATES = 0,
+        GROUP_TEMPLATES_CONTIGUOUS = 1,
+        GROUP_FRAMES = 2
+    };
+    static std::vector<unsigned char> groupUniqueId();
+    void setGroup(int n_ranks, int rank, const std::vector<unsigned char> &unique_id, GroupMode mode = GROUP_TEMPLATES);
+    int groupSize() const { return group_n_; }
+
 protected:
     cv::Ptr<ColorGradient> modality;
     int pyramid_levels;
@@ -247,6 +265,7 @@ private:
     mutable bool templates_dirty_;
     mutable std::vector<std::string> slots_; // class id of every uploaded class slot (std::map order)
     int device_;
+    int group_n_ = 0, group_mode_ = -1; // 0: not in a group
 };
 
 } // namespace line2Dup
@@ -290,29 +309,24 @@ public:
             this->mask = mask;
     }
 
-    // this fork: right-angle rotations + resize only (line2Dup.h:379-405)
+    // this fork: right-angle rotations + resize only (line2Dup.h:379-405): an angle within ANGLE_TOLERANCE of 90, 180
+    // or 270 degrees turns the image by that quarter, any other angle leaves it as it is; then cv::resize by `scale`
     static cv::Mat transform(cv::Mat src, float angle, float scale)
     {
+        static const struct
+        {
+            double degrees;
+            int code;
+        } quarter[3] = {{90.0, cv::ROTATE_90_CLOCKWISE}, {180.0, cv::ROTATE_180}, {270.0, cv::ROTATE_90_COUNTERCLOCKWISE}};
+        cv::Mat turned = src;
+        for (const auto &q : quarter)
+            if (std::abs(angle - q.degrees) < ANGLE_TOLERANCE)
+            {
+                cv::rotate(src, turned, q.code);
+                break;
+            }
         cv::Mat dst;
-        if (std::abs(angle - 90.0) < ANGLE_TOLERANCE)
-        {
-            cv::rotate(src, dst, cv::ROTATE_90_CLOCKWISE);
-            cv::resize(dst, dst, cv::Size(), scale, scale);
-        }
-        else if (std::abs(angle - 180.0) < ANGLE_TOLERANCE)
-        {
-            cv::rotate(src, dst, cv::ROTATE_180);
-            cv::resize(dst, dst, cv::Size(), scale, scale);
-        }
-        else if (std::abs(angle - 270.0) < ANGLE_TOLERANCE)
-        {
-            cv::rotate(src, dst, cv::ROTATE_90_COUNTERCLOCKWISE);
-            cv::resize(dst, dst, cv::Size(), scale, scale);
-        }
-        else
-        {
-            cv::resize(src, dst, cv::Size(), scale, scale);
-        }
+        cv::resize(turned, dst, cv::Size(), scale, scale);
         return dst;
     }
 

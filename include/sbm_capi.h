@@ -21,6 +21,10 @@
  *   sbm_similarity_map      similarity / similarity_64                                line2Dup.cpp:807-858,924-984
  *   sbm_similarity_local    similarityLocal / similarityLocal_64                      line2Dup.cpp:860-922,986-1048
  *   sbm_merge_shard_records the `matches.insert(...)` reduction over templates + sort/unique, across GPUs   line2Dup.cpp:1124-1145,1166-1170
+ *   sbm_group_create / sbm_group_match[_batch][_device]  Detector::match with the template loop (`#pragma omp parallel for`,
+ *                           line2Dup.cpp:1166-1170) or the caller's frame loop (test_jabil.cpp:314-374) spread over the GPUs
+ *                           of one box: one context per GPU, one ncclAllGather of the compact record lists
+ *   sbm_set_candidate_capacity  the `std::vector<Match> candidates` of matchClass (unbounded there)       line2Dup.cpp:1160-1216
  *   sbm_quantized_orientations  quantizedOrientations + hysteresisGradient + pyrDown (training)  line2Dup.cpp:218-444
  */
 #ifndef SBM_CAPI_H
@@ -87,6 +91,11 @@ int sbm_set_class_templates(sbm_ctx *ctx, int class_idx, int n_templates, const 
                             const sbm_feature *feats);
 int sbm_clear_templates(sbm_ctx *ctx);
 int sbm_num_templates(sbm_ctx *ctx, int class_idx);
+/* Records each stage of a frame may hold inside the context (default 65536 per frame slot).  The host entry points
+ * (sbm_match, sbm_match_batch, sbm_group_match*) grow these buffers and re-run a frame that overflowed them; the
+ * device-resident entry points never synchronise, so they raise the overflow flag instead (d_count[1], block header) --
+ * the caller then re-runs the frame through sbm_match or after raising the capacity here. */
+int sbm_set_candidate_capacity(sbm_ctx *ctx, int records);
 
 /* Detector::match.  img: 8-bit, channels 1 or 3 (interleaved), `stride` bytes per row (0 = packed);
  * w,h must satisfy the reference's asserts at every level (h_l % T_l == 0, w_l % T_l == 0,
@@ -118,7 +127,9 @@ int sbm_match_batch(sbm_ctx *ctx, const uint8_t *const *imgs, const uint8_t *con
  * enqueued on `stream` (a cudaStream_t, or NULL for the context's own stream) and nothing is copied to
  * the host.  Results stay on the device:
  *   d_records: sbm_device_rec[cap]   (unordered; see sbm_device_rec)
- *   d_count  : uint32[2]             ([0] = number of records produced (may exceed cap), [1] = overflow flag)
+ *   d_count  : uint32[2]             ([0] = number of records produced (may exceed cap), [1] = overflow flag: the list
+ *                                     is incomplete because cap, or the context's own per-stage candidate capacity
+ *                                     (sbm_set_candidate_capacity), was too small)
  * Either may be NULL, in which case the context's internal buffers are used (sbm_device_results). */
 typedef struct sbm_device_rec {
     int32_t x, y;          /* level-0 top-left of the match */
@@ -150,10 +161,55 @@ int sbm_finalize_records(sbm_ctx *ctx, const sbm_device_rec *recs, int n, const 
  *   mode         SBM_SHARD_INTERLEAVED: rank r holds global ids r, r+G, r+2G, ... of every class;
  *                SBM_SHARD_CONTIGUOUS : rank r holds the block that follows the blocks of ranks < r
  * Output as sbm_finalize_records: the reference's serial candidate order over GLOBAL template ids, then
- * (finalize != 0) Detector::match's std::sort + std::unique (line2Dup.cpp:1143-1145). */
+ * (finalize != 0) Detector::match's std::sort + std::unique (line2Dup.cpp:1143-1145).
+ * class_order[n_order]: the caller's class list (class slots, repeats allowed, entries outside 0..n_classes-1 skipped):
+ *                the reference appends class by class in that order (:1124-1140); NULL / 0 = every class slot once, ascending. */
 enum { SBM_SHARD_INTERLEAVED = 0, SBM_SHARD_CONTIGUOUS = 1 };
 int sbm_merge_shard_records(const sbm_device_rec *recs, const int *n_per_rank, int n_ranks, const int *class_sizes, int n_classes,
-                            int mode, int finalize, sbm_match_rec *out, int cap, int *n_out);
+                            int mode, const int *class_order, int n_order, int finalize, sbm_match_rec *out, int cap, int *n_out);
+
+/* ---- Multi-GPU group: one context per GPU (one process or thread each), NCCL over NVLink / NVSwitch -------------------
+ * The path shards two ways, both with ONE exchange of KBs per batch:
+ *   SBM_GROUP_TEMPLATES[_CONTIGUOUS]  every rank is handed the SAME frames and the FULL classes (sbm_set_class_templates
+ *        keeps this rank's slice: ids rank, rank + n, ... or its contiguous block); each rank builds the frames' linear
+ *        memories and matches its slice; the merged list of a frame is identical, on every rank, to the unsharded sbm_match.
+ *   SBM_GROUP_FRAMES  every rank holds all templates and its OWN frames; the per-frame lists of all ranks are gathered.
+ * A frame's result travels as one block of sbm_group_block_bytes(cap) bytes: {uint32 count, uint32 overflow, 0, 0} followed
+ * by cap sbm_device_rec; the ranks' blocks are exchanged with one ncclAllGather on the stream the kernels ran on (counts
+ * and records in one buffer).  libnccl.so.2 is bound at run time on the first sbm_group_* call (the copy already loaded in
+ * the process, else the system's; SBM_NCCL_LIB overrides); single-GPU callers never need it.
+ *
+ * Set-up: rank 0 calls sbm_group_unique_id and hands the 128 bytes to the other ranks by any means (file, pipe, MPI,
+ * torch.distributed ...); every rank then calls sbm_group_create (collective: returns when all n ranks have called it),
+ * and only then installs its templates.  All sbm_group_match* calls are collective: every rank makes the same call with
+ * the same n_frames, threshold, class list and capacities. */
+enum { SBM_GROUP_TEMPLATES = 0, SBM_GROUP_TEMPLATES_CONTIGUOUS = 1, SBM_GROUP_FRAMES = 2 };
+#define SBM_GROUP_ID_BYTES 128
+int sbm_group_unique_id(void *id128);
+int sbm_group_create(sbm_ctx *ctx, int n_ranks, int rank, const void *id128, int mode);
+int sbm_group_destroy(sbm_ctx *ctx);
+/* returns 1 when the context belongs to a group (and fills what is non-NULL), 0 when not */
+int sbm_group_info(sbm_ctx *ctx, int *n_ranks, int *rank, int *mode);
+/* Detector::match over the group, template sharding: same arguments and same result as sbm_match, on every rank. */
+int sbm_group_match(sbm_ctx *ctx, const uint8_t *img, int w, int h, int channels, size_t stride, const uint8_t *mask,
+                    float threshold, const int *class_idx, int n_classes, sbm_match_rec *out, int cap, int *n_out);
+/* sbm_match_batch over the group.  Template sharding: every rank passes the same n_frames frames; out / frame_begin
+ * describe n_frames lists.  Frame sharding: every rank passes its own n_frames frames (the same count on every rank); out /
+ * frame_begin describe n_ranks * n_frames lists, rank-major (list r * n_frames + f = frame f of rank r), on every rank.
+ * Internal block and stage capacities grow (on all ranks alike) when a frame overflows them. */
+int sbm_group_match_batch(sbm_ctx *ctx, const uint8_t *const *imgs, const uint8_t *const *masks, int n_frames, int w, int h,
+                          int channels, size_t stride, float threshold, const int *class_idx, int n_classes, sbm_match_rec *out,
+                          int cap, int *frame_begin);
+/* Device-resident and asynchronous: the frames (d_imgs + i * frame_stride) are matched on the context's frame slots, the
+ * n_frames result blocks are allgathered on `stream` into d_gathered = uint8 [n_ranks][n_frames][sbm_group_block_bytes(cap)]
+ * and nothing is copied to the host.  sbm_group_finalize turns a host copy of d_gathered into the final lists (as
+ * sbm_group_match_batch lays them out); it fails with SBM_ERR_CAPACITY when a block's overflow flag is set. */
+size_t sbm_group_block_bytes(int cap_per_frame);
+int sbm_group_match_batch_device(sbm_ctx *ctx, const void *d_imgs, size_t frame_stride, int n_frames, int w, int h, int channels,
+                                 float threshold, const int *class_idx, int n_classes, void *d_gathered, int cap_per_frame,
+                                 void *stream);
+int sbm_group_finalize(sbm_ctx *ctx, const void *h_gathered, int n_frames, int cap_per_frame, const int *class_idx, int n_classes,
+                       int finalize, sbm_match_rec *out, int cap, int *frame_begin);
 
 /* Copy an intermediate of the most recent frame to host memory `dst` (`bytes` must match exactly;
  * pass dst == NULL to query the size through *bytes_needed).  SPREAD and RESPONSE are only materialised

@@ -18,7 +18,12 @@ SYMBOLS = [
     "sbm_num_templates", "sbm_match", "sbm_match_candidates", "sbm_match_device", "sbm_device_results",
     "sbm_finalize_records", "sbm_set_debug", "sbm_get_intermediate", "sbm_similarity_map", "sbm_similarity_local",
     "sbm_last_stats", "sbm_last_timing", "sbm_set_timing", "sbm_match_batch", "sbm_match_batch_device", "sbm_time_similarity", "sbm_time_kernels", "sbm_quantized_orientations", "sbm_merge_shard_records", "sbm_time_l2_read",
+    "sbm_set_candidate_capacity", "sbm_group_unique_id", "sbm_group_create", "sbm_group_destroy", "sbm_group_info", "sbm_group_match",
+    "sbm_group_match_batch", "sbm_group_block_bytes", "sbm_group_match_batch_device", "sbm_group_finalize",
 ]
+
+GROUP_TEMPLATES, GROUP_TEMPLATES_CONTIGUOUS, GROUP_FRAMES = 0, 1, 2
+GROUP_ID_BYTES = 128
 
 SBM_QUANTIZED, SBM_SPREAD, SBM_RESPONSE, SBM_LINEAR, SBM_PYRAMID_SRC = range(5)
 
@@ -60,7 +65,18 @@ def lib():
         L.sbm_device_results.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(ci)]
         L.sbm_finalize_records.argtypes = [vp, vp, ci, vp, ci, ci, vp, ci, C.POINTER(ci)]
         L.sbm_time_l2_read.argtypes = [vp, C.c_size_t, ci, C.POINTER(cf)]
-        L.sbm_merge_shard_records.argtypes = [vp, vp, ci, vp, ci, ci, ci, vp, ci, C.POINTER(ci)]
+        L.sbm_merge_shard_records.argtypes = [vp, vp, ci, vp, ci, ci, vp, ci, ci, vp, ci, C.POINTER(ci)]
+        L.sbm_set_candidate_capacity.argtypes = [vp, ci]
+        L.sbm_group_unique_id.argtypes = [vp]
+        L.sbm_group_create.argtypes = [vp, ci, ci, vp, ci]
+        L.sbm_group_destroy.argtypes = [vp]
+        L.sbm_group_info.argtypes = [vp, C.POINTER(ci), C.POINTER(ci), C.POINTER(ci)]
+        L.sbm_group_match.argtypes = margs
+        L.sbm_group_match_batch.argtypes = [vp, vp, vp, ci, ci, ci, ci, C.c_size_t, cf, vp, ci, vp, ci, vp]
+        L.sbm_group_block_bytes.argtypes = [ci]
+        L.sbm_group_block_bytes.restype = C.c_size_t
+        L.sbm_group_match_batch_device.argtypes = [vp, vp, C.c_size_t, ci, ci, ci, ci, cf, vp, ci, vp, ci, vp]
+        L.sbm_group_finalize.argtypes = [vp, vp, ci, ci, vp, ci, ci, vp, ci, vp]
         L.sbm_set_debug.argtypes = [vp, ci]
         L.sbm_set_timing.argtypes = [vp, ci]
         L.sbm_get_intermediate.argtypes = [vp, ci, ci, vp, C.c_size_t, C.POINTER(C.c_size_t)]

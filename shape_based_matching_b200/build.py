@@ -36,7 +36,7 @@ def _stale(target, sources):
 
 
 def build_cuda(force=False):
-    srcs = [os.path.join(PKG, "csrc", f) for f in ("sbm_capi.cu", "sbm_kernels.cuh")] + [
+    srcs = [os.path.join(PKG, "csrc", f) for f in ("sbm_capi.cu", "sbm_kernels.cuh", "sbm_nccl.hpp")] + [
         os.path.join(ROOT, "include", "sbm_capi.h")
     ]
     if force or _stale(LIB, srcs):
@@ -55,14 +55,20 @@ def build_host(force=False):
     """The drop-in C++ API (include/line2Dup.h) over the C ABI, and the C++ test driver that uses it."""
     inc = os.path.join(ROOT, "include")
     src = os.path.join(PKG, "csrc", "line2Dup.cpp")
-    deps = [src, os.path.join(inc, "line2Dup.h"), os.path.join(inc, "sbm_capi.h"), os.path.join(inc, "sbm", "cv_compat.hpp"),
+    src_c = os.path.join(PKG, "csrc", "line2Dup_c.cpp")
+    deps = [src, src_c, os.path.join(inc, "line2Dup.h"), os.path.join(inc, "sbm_capi.h"), os.path.join(inc, "sbm", "cv_compat.hpp"),
             os.path.join(inc, "sbm", "imgproc_compat.hpp"), LIB]
     if force or _stale(HOST_LIB, deps):
-        _run([HOST_CXX, "-std=c++17", "-O2", "-fPIC", "-shared", "-Wall", "-I" + inc, src, "-o", HOST_LIB, "-L" + PKG, "-lsbm_b200", "-lz",
+        _run([HOST_CXX, "-std=c++17", "-O2", "-fPIC", "-shared", "-Wall", "-I" + inc, src, src_c, "-o", HOST_LIB, "-L" + PKG, "-lsbm_b200", "-lz",
               "-Wl,-rpath,$ORIGIN"])
     drv = os.path.join(ROOT, "tests", "cpp", "dropin_driver.cpp")
     if os.path.exists(drv) and (force or _stale(DRIVER, [drv, HOST_LIB])):
         _run([HOST_CXX, "-std=c++17", "-O2", "-Wall", "-I" + inc, drv, "-o", DRIVER, "-L" + PKG, "-lline2Dup_b200", "-lsbm_b200", "-lz",
+              "-Wl,-rpath,$ORIGIN/../../shape_based_matching_b200"])
+    gdrv = os.path.join(ROOT, "tests", "cpp", "group_driver.cpp")
+    gbin = os.path.join(ROOT, "tests", "cpp", "group_driver")
+    if os.path.exists(gdrv) and (force or _stale(gbin, [gdrv, HOST_LIB])):
+        _run([HOST_CXX, "-std=c++17", "-O2", "-Wall", "-I" + inc, gdrv, "-o", gbin, "-L" + PKG, "-lline2Dup_b200", "-lsbm_b200", "-lz", "-pthread",
               "-Wl,-rpath,$ORIGIN/../../shape_based_matching_b200"])
     return HOST_LIB
 

@@ -38,24 +38,39 @@ int labelOf(int quantized)
 
 // process-wide context used by the training front end (ColorGradientPyramid carries no Detector pointer in the
 // reference's interface).  weak_threshold only gates the vote, it is passed per call through a context per value.
+// Guarded by g_train_mu (Detector::setDevice may run on another thread); the cached contexts are destroyed at exit.
 std::mutex g_train_mu;
-std::map<std::pair<int, float>, sbm_ctx *> g_train_ctx;
 int g_train_device = 0;
+struct TrainContexts
+{
+    std::map<std::pair<int, float>, sbm_ctx *> ctx;
+    ~TrainContexts()
+    {
+        for (auto &kv : ctx)
+            sbm_destroy(kv.second);
+    }
+} g_train;
 
 sbm_ctx *trainingContext(float weak)
 {
     std::lock_guard<std::mutex> lock(g_train_mu);
     auto key = std::make_pair(g_train_device, weak);
-    auto it = g_train_ctx.find(key);
-    if (it != g_train_ctx.end())
+    auto it = g_train.ctx.find(key);
+    if (it != g_train.ctx.end())
         return it->second;
     const int T[2] = {4, 8};
     sbm_ctx *c = nullptr;
     int rc = sbm_create(T, 2, weak, 60.f, 63, g_train_device, &c);
     if (rc)
         throwSbm(rc, "sbm_create");
-    g_train_ctx[key] = c;
+    g_train.ctx[key] = c;
     return c;
+}
+
+void setTrainingDevice(int device)
+{
+    std::lock_guard<std::mutex> lock(g_train_mu);
+    g_train_device = device;
 }
 
 Mat continuous8u(const Mat &m)
@@ -148,30 +163,35 @@ void ColorGradient::write(FileStorage &fs) const
 ColorGradientPyramid::ColorGradientPyramid(const Mat &_src, const Mat &_mask, float _weak_threshold, size_t _num_features,
                                            float _strong_threshold)
     : src(_src), mask(_mask), pyramid_level(0), weak_threshold(_weak_threshold), num_features(_num_features),
-      strong_threshold(_strong_threshold), src0(continuous8u(_src))
+      strong_threshold(_strong_threshold)
 {
     CV_Assert(src.channels() == 1 || src.channels() == 3);
     update();
 }
 
-// quantizedOrientations + hysteresisGradient (:218-404) of the current level, on the GPU
-void ColorGradientPyramid::update()
+// quantizedOrientations + hysteresisGradient (:218-404) on the GPU.  steps = 0: of `src` as it is (constructor);
+// steps = 1: of cv::pyrDown(src) (:431-433), which also becomes the new `src` -- one level per call, the chain is
+// never recomputed from level 0.
+void ColorGradientPyramid::update() { updateFrom(0); }
+
+void ColorGradientPyramid::updateFrom(int steps)
 {
-    int w = src0.cols, h = src0.rows;
-    for (int l = 0; l < pyramid_level; ++l)
+    const Mat cur = continuous8u(src);
+    int w = cur.cols, h = cur.rows;
+    for (int l = 0; l < steps; ++l)
         w /= 2, h /= 2;
     magnitude.create(h, w, CV_32FC1);
     angle_ori.create(h, w, CV_32FC1);
     angle.create(h, w, CV_8UC1);
-    Mat level_src(h, w, src0.type());
+    Mat level_src(h, w, cur.type());
     int wo = 0, ho = 0;
-    int rc = sbm_quantized_orientations(trainingContext(weak_threshold), src0.data, src0.cols, src0.rows, src0.channels(), src0.step,
-                                        pyramid_level, magnitude.ptr<float>(), angle_ori.ptr<float>(), angle.data, level_src.data, &wo,
+    int rc = sbm_quantized_orientations(trainingContext(weak_threshold), cur.data, cur.cols, cur.rows, cur.channels(), cur.step, steps,
+                                        magnitude.ptr<float>(), angle_ori.ptr<float>(), angle.data, steps ? level_src.data : nullptr, &wo,
                                         &ho);
     if (rc)
         throwSbm(rc, "sbm_quantized_orientations");
     CV_Assert(wo == w && ho == h);
-    if (pyramid_level > 0)
+    if (steps > 0)
         src = level_src;
 }
 
@@ -187,7 +207,7 @@ void ColorGradientPyramid::pyrDown()
         resize(mask, next_mask, size, 0.0, 0.0, INTER_NEAREST);
         mask = next_mask;
     }
-    update(); // cv::pyrDown of the image happens on the device, inside the chain from src0
+    updateFrom(1); // cv::pyrDown of the image happens on the device
     CV_Assert(src.cols == size.width && src.rows == size.height);
 }
 
@@ -378,7 +398,29 @@ void Detector::setDevice(int device)
 {
     CV_Assert(!ctx_);
     device_ = device;
-    g_train_device = device;
+    setTrainingDevice(device);
+}
+
+std::vector<unsigned char> Detector::groupUniqueId()
+{
+    std::vector<unsigned char> id(SBM_GROUP_ID_BYTES);
+    int rc = sbm_group_unique_id(id.data());
+    if (rc)
+        throwSbm(rc, "sbm_group_unique_id");
+    return id;
+}
+
+void Detector::setGroup(int n_ranks, int rank, const std::vector<unsigned char> &unique_id, GroupMode mode)
+{
+    CV_Assert(unique_id.size() == SBM_GROUP_ID_BYTES && group_n_ == 0);
+    sbm_ctx *c = context();
+    int rc = sbm_clear_templates(c); // template sharding keeps a slice of every class: they are re-installed below
+    if (!rc)
+        rc = sbm_group_create(c, n_ranks, rank, unique_id.data(), (int)mode);
+    if (rc)
+        throwSbm(rc, "sbm_group_create");
+    group_n_ = n_ranks, group_mode_ = (int)mode;
+    templates_dirty_ = true;
 }
 
 sbm_ctx *Detector::context() const
@@ -461,8 +503,11 @@ std::vector<Match> Detector::match(Mat source, float threshold, const std::vecto
     int n = 0;
     for (;;)
     {
-        int rc = sbm_match(ctx_, img.data, img.cols, img.rows, img.channels(), img.step, m8.empty() ? nullptr : m8.data, threshold,
-                           idx.empty() ? nullptr : idx.data(), (int)idx.size(), recs.data(), (int)recs.size(), &n);
+        // in a template-sharding group the same call runs on every rank and returns the merged list (sbm_group_match)
+        const bool sharded = group_n_ > 0 && group_mode_ != GROUP_FRAMES;
+        int rc = (sharded ? sbm_group_match : sbm_match)(ctx_, img.data, img.cols, img.rows, img.channels(), img.step,
+                                                         m8.empty() ? nullptr : m8.data, threshold, idx.empty() ? nullptr : idx.data(),
+                                                         (int)idx.size(), recs.data(), (int)recs.size(), &n);
         if (rc == SBM_ERR_CAPACITY && n > (int)recs.size())
         {
             recs.resize(n);
@@ -482,7 +527,8 @@ std::vector<Match> Detector::match(Mat source, float threshold, const std::vecto
 std::vector<std::vector<Match>> Detector::matchBatch(const std::vector<Mat> &sources, float threshold,
                                                      const std::vector<std::string> &class_ids) const
 {
-    std::vector<std::vector<Match>> out(sources.size());
+    const size_t lists = sources.size() * (group_n_ > 0 && group_mode_ == GROUP_FRAMES ? group_n_ : 1);
+    std::vector<std::vector<Match>> out(lists);
     if (sources.empty())
         return out;
     syncTemplates();
@@ -497,23 +543,25 @@ std::vector<std::vector<Match>> Detector::matchBatch(const std::vector<Mat> &sou
     const std::vector<int> idx = slotsOf(slots_, class_ids);
     if (!class_ids.empty() && std::all_of(idx.begin(), idx.end(), [](int v) { return v < 0; }))
         return out;
-    const int n = (int)sources.size();
-    std::vector<sbm_match_rec> recs((size_t)256 * n);
-    std::vector<int> begin(n + 1);
+    const int n = (int)sources.size(), nl = (int)lists;
+    std::vector<sbm_match_rec> recs((size_t)256 * nl);
+    std::vector<int> begin(nl + 1);
     for (;;)
     {
-        int rc = sbm_match_batch(ctx_, ptrs.data(), nullptr, n, imgs[0].cols, imgs[0].rows, imgs[0].channels(), imgs[0].step, threshold,
-                                 idx.empty() ? nullptr : idx.data(), (int)idx.size(), recs.data(), (int)recs.size(), begin.data());
-        if (rc == SBM_ERR_CAPACITY && begin[n] > (int)recs.size())
+        int rc = (group_n_ > 0 ? sbm_group_match_batch : sbm_match_batch)(ctx_, ptrs.data(), nullptr, n, imgs[0].cols, imgs[0].rows,
+                                                                          imgs[0].channels(), imgs[0].step, threshold,
+                                                                          idx.empty() ? nullptr : idx.data(), (int)idx.size(), recs.data(),
+                                                                          (int)recs.size(), begin.data());
+        if (rc == SBM_ERR_CAPACITY && begin[nl] > (int)recs.size())
         {
-            recs.resize(begin[n]);
+            recs.resize(begin[nl]);
             continue;
         }
         if (rc)
             throwSbm(rc, "sbm_match_batch");
         break;
     }
-    for (int f = 0; f < n; ++f)
+    for (int f = 0; f < nl; ++f)
         for (int i = begin[f]; i < begin[f + 1]; ++i)
             out[f].emplace_back(recs[i].x, recs[i].y, recs[i].similarity, slots_[recs[i].class_idx], recs[i].template_id);
     return out;

@@ -12,6 +12,7 @@
 // implementation of any pipeline stage in this library.
 #include "sbm_capi.h"
 #include "sbm_kernels.cuh"
+#include "sbm_nccl.hpp"
 
 #include <algorithm>
 #include <cstdarg>
@@ -62,21 +63,18 @@ int frameSlots()
     }();
     return n;
 }
-#ifndef SBM_TALL_MIN
-#define SBM_TALL_MIN (2 * 148)
-#endif
 constexpr int COUNT_WORDS = 16; // [0..levels-1] stage counts, [10..11] u64 local evaluations
 constexpr uint32_t HEAD_RECS = 1024;
 
 // K1 tile height for a w x h level: 64x32 tiles unless that leaves the GPU under two CTAs per SM, then 64x16.
-// SBM_ORIENT_TH=8|16|28|32 forces one height (experiments).
-int orientTileH(int w, int h)
+// SBM_ORIENT_TH=8|16|28|32 forces one height (experiments).  sms: multiprocessors of the context's device.
+int orientTileH(int w, int h, int sms)
 {
     static const int forced = getenv("SBM_ORIENT_TH") ? atoi(getenv("SBM_ORIENT_TH")) : 0;
     if (forced == 8 || forced == 16 || forced == 28 || forced == 32)
         return forced;
     const int cols = (w + K1_TW - 1) / K1_TW;
-    if (cols * ((h + 31) / 32) >= SBM_TALL_MIN)
+    if (cols * ((h + 31) / 32) >= 2 * sms)
         return 32;
     // 64x28 tiles fill the 148 SMs evenly at 1024 rows (592 CTAs = 4 per SM; the kernel alone 13.6 -> 12.5 us) but the
     // frame as a whole got no faster (graph 52.2 -> 52.8 us, 23.2 -> 23.5 us per frame in flight): not used
@@ -91,10 +89,10 @@ void *orientFunc(int ch, int th)
 }
 
 // one K1 launch on stream st (match path: no dump outputs)
-cudaError_t launchOrient(int ch, const uint8_t *src, int w, int h, const uint8_t *mask, int mask_shift, int mask_w, float weak_sq,
+cudaError_t launchOrient(int sms, int ch, const uint8_t *src, int w, int h, const uint8_t *mask, int mask_shift, int mask_w, float weak_sq,
                          uint8_t *quant, cudaStream_t st)
 {
-    const int th = orientTileH(w, h);
+    const int th = orientTileH(w, h, sms);
     float *nf = nullptr;
     void *argv[] = {&src, &w, &h, &mask, &mask_shift, &mask_w, &weak_sq, &quant, &nf, &nf};
     return cudaLaunchKernel(orientFunc(ch, th), dim3((w + K1_TW - 1) / K1_TW, (h + th - 1) / th), dim3(K1_THREADS), argv, 0, st);
@@ -181,6 +179,8 @@ struct Slot
 struct sbm_ctx
 {
     int device = 0;
+    int sms = 148;                 // multiprocessors of `device`
+    int refine_grid[2] = {0, 0};   // K5b grid (flat / tiled kernel) = CTAs resident at once on `device`
     std::vector<int> T;
     float weak = 30.f, strong = 60.f;
     int num_features = 63;
@@ -216,6 +216,20 @@ struct sbm_ctx
     bool debug = false, timing = false;
     float last_ms[4] = {0, 0, 0, 0};
     uint64_t stats[8] = {0};
+
+    // multi-GPU group (sbm_group_*): this context is rank `rank` of `n` contexts, one per GPU, one NCCL communicator
+    struct Group
+    {
+        bool on = false;
+        int n = 1, rank = 0, mode = 0;
+        NcclApi::comm_t comm = nullptr;
+        std::vector<int> global_n;  // template modes: size of the FULL class per class slot (this rank keeps a slice)
+        uint8_t *d_send = nullptr, *d_recv = nullptr; // [n_frames] / [n][n_frames] result blocks (header + records)
+        size_t send_alloc = 0, recv_alloc = 0;
+        uint8_t *h_recv = nullptr; // pinned copy of d_recv
+        size_t h_alloc = 0;
+        uint32_t cap = 256; // records per frame block of the host-side group calls (grown on overflow)
+    } group;
 };
 
 namespace
@@ -315,26 +329,20 @@ int ensureShape(sbm_ctx *c, int w, int h, int ch)
 }
 
 // K5b walks the candidate list grid-stride with a static split, so the grid is exactly the number of CTAs that are
-// resident at once (a CTA that starts after the others have finished would do its whole share alone)
-int refineGrid(bool tiled = false)
+// resident at once on the context's device (a CTA that starts after the others have finished would do its whole share
+// alone).  Computed once per context in sbm_create, for c->device.
+int computeRefineGrid(int sms, bool tiled)
 {
-    static int grids[2] = {0, 0};
-    int &grid = grids[tiled ? 1 : 0];
-    if (!grid)
-    {
-        int dev = 0, sms = 148, per_sm = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        const cudaError_t e = tiled ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_refine_tiled, K6_THREADS, 0)
-                                    : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_refine, K6_THREADS, 0);
-        if (e != cudaSuccess || per_sm < 1)
-            per_sm = 1;
-        if (const char *ev = getenv("SBM_REFINE_CTAS_PER_SM"))
-            per_sm = std::max(1, atoi(ev));
-        grid = sms * per_sm;
-    }
-    return grid;
+    int per_sm = 0;
+    const cudaError_t e = tiled ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_refine_tiled, K6_THREADS, 0)
+                                : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_refine, K6_THREADS, 0);
+    if (e != cudaSuccess || per_sm < 1)
+        per_sm = 1;
+    if (const char *ev = getenv("SBM_REFINE_CTAS_PER_SM"))
+        per_sm = std::max(1, atoi(ev));
+    return sms * per_sm;
 }
+int refineGrid(const sbm_ctx *c, bool tiled) { return c->refine_grid[tiled ? 1 : 0]; }
 
 // the slot's stream and its events are created together (the timers rely on the events)
 int ensureStream(Slot &s)
@@ -602,6 +610,24 @@ cudaError_t launchRefine(bool tiled, int grid, const uint8_t *lm, const TemplLev
                          uint32_t in_cap, Cand *out, uint32_t *out_count, uint32_t out_cap, int w, int h, int T, float threshold, uint16_t *dump,
                          int raw_center, unsigned long long *local_evals, cudaStream_t st);
 
+// ---- template sharding arithmetic ----
+// templates of a class of n owned by `rank` of `world`: interleaved ids rank, rank + world, ...; or the contiguous block
+// that follows the blocks of the lower ranks (blocks differ by at most one template)
+int shardCount(int n, int rank, int world, int mode)
+{
+    if (mode == SBM_SHARD_INTERLEAVED)
+        return n > rank ? (n - rank + world - 1) / world : 0;
+    return n / world + (rank < n % world ? 1 : 0);
+}
+int shardBegin(int n, int rank, int world) { return rank * (n / world) + std::min(rank, n % world); } // contiguous mode
+bool shardOwns(int t, int n, int rank, int world, int mode)
+{
+    if (mode == SBM_SHARD_INTERLEAVED)
+        return t % world == rank;
+    const int b = shardBegin(n, rank, world);
+    return t >= b && t < b + shardCount(n, rank, world, mode);
+}
+
 int prepare(sbm_ctx *c, Slot &s, int w, int h, int ch, const int *class_idx, int n_classes)
 {
     int rc;
@@ -640,7 +666,7 @@ int enqueueFrame(sbm_ctx *c, Slot &s, const uint8_t *d_img, const uint8_t *d_mas
             src = LB.d_src;
             ++launches;
         }
-        CK(launchOrient(c->c, src, G.w, G.h, d_mask, l, c->w, weak_sq, LB.d_quant, st));
+        CK(launchOrient(c->sms, c->c, src, G.w, G.h, d_mask, l, c->w, weak_sq, LB.d_quant, st));
         uint8_t *ds = c->debug ? LB.d_spread : nullptr, *dr = c->debug ? LB.d_resp : nullptr;
         CK(launchSpread(G, LB.d_quant, LB.d_lm, ds, dr, st));
         launches += 2;
@@ -676,11 +702,17 @@ int enqueueFrame(sbm_ctx *c, Slot &s, const uint8_t *d_img, const uint8_t *d_mas
         out_cnt = (last && user_count) ? user_count : s.d_counts + stage;
         if (c->n_active > 0)
         {
-            CK(launchRefine(G.tiled, refineGrid(G.tiled), s.lv[l].d_lm, c->tl[l].d_tl, c->tl[l].d_feats, in, in_cnt, in_cap, out, out_cnt, out_cap, G.w,
+            CK(launchRefine(G.tiled, refineGrid(c, G.tiled), s.lv[l].d_lm, c->tl[l].d_tl, c->tl[l].d_feats, in, in_cnt, in_cap, out, out_cnt, out_cap, G.w,
                             G.h, G.T, threshold, nullptr, 0, reinterpret_cast<unsigned long long *>(s.d_counts + 10), st));
             ++launches;
         }
         in = out, in_cap = out_cap, in_cnt = out_cnt;
+    }
+    if (user_count)
+    {
+        // stages 0 .. L-2 counted in the slot's counters (the last one in user_count[0] itself)
+        k_overflow_flag<<<1, 1, 0, st>>>(user_count, user_cap, s.d_counts, L - 1, s.cap);
+        ++launches;
     }
     if (c->timing)
         CK(cudaEventRecord(s.ev[2], st));
@@ -809,7 +841,7 @@ int buildGraph(sbm_ctx *c, Slot &s, const uint8_t *src0, float threshold, bool w
             dep_src.assign(1, n_pyr);
             ++launches;
         }
-        const int th = orientTileH(G.w, G.h);
+        const int th = orientTileH(G.w, G.h, c->sms);
         dim3 g1((G.w + K1_TW - 1) / K1_TW, (G.h + th - 1) / th);
         cudaGraphNode_t n_or, n_sp;
         int mask_shift = l, mask_w = c->w;
@@ -864,7 +896,7 @@ int buildGraph(sbm_ctx *c, Slot &s, const uint8_t *src0, float threshold, bool w
             int raw_center = 0;
             unsigned long long *ev = reinterpret_cast<unsigned long long *>(s.d_counts + 10);
             cudaGraphNode_t n_ref;
-            if ((rc = addKernel(g, &n_ref, {tail, spread_node[l]}, refineFunc(G.tiled), dim3(refineGrid(G.tiled)), dim3(K6_THREADS), lm, tl, ff, cin, cin_cnt, in_cap,
+            if ((rc = addKernel(g, &n_ref, {tail, spread_node[l]}, refineFunc(G.tiled), dim3(refineGrid(c, G.tiled)), dim3(K6_THREADS), lm, tl, ff, cin, cin_cnt, in_cap,
                                 out, out_cnt, out_cap, G.w, G.h, G.T, threshold, nodump, raw_center, ev)))
                 return rc;
             tail = n_ref;
@@ -954,13 +986,14 @@ int runFrame(sbm_ctx *c, Slot &s, const uint8_t *d_img, const uint8_t *d_mask, f
     return with_fetch ? enqueueFetch(s, st) : 0;
 }
 
-int exportResults(Slot &s, cudaStream_t st, void *d_records, uint32_t cap, void *d_count)
+int exportResults(sbm_ctx *c, Slot &s, cudaStream_t st, void *d_records, uint32_t cap, void *d_count)
 {
     if (!d_records && !d_count)
         return 0;
     if (!d_records || !d_count)
         return fail(SBM_ERR_BAD_ARG, "d_records and d_count must be given together");
-    k_export<<<8, 256, 0, st>>>(s.d_final, s.d_final_count, s.final_cap, (Cand *)d_records, cap, (uint32_t *)d_count);
+    k_export<<<8, 256, 0, st>>>(s.d_final, s.d_final_count, s.final_cap, (Cand *)d_records, cap, (uint32_t *)d_count, s.d_counts, c->levels,
+                                s.cap);
     ++s.launches;
     CK(cudaGetLastError());
     return 0;
@@ -1169,6 +1202,352 @@ int finishBatchFrame(sbm_ctx *c, Slot &s, const uint8_t *dm, float threshold, bo
     }
     return fail(SBM_ERR_CAPACITY, "candidate buffers keep overflowing");
 }
+// Template sharding: the merge step after the allgather.  Pure host code, no context.  The reference appends
+// candidates class by class in the caller's order (repeats included, line2Dup.cpp:1124-1140), within a class by
+// template_id ascending and coarse scan order (:1170, :1200-1216); so the ranks' records are re-labelled with GLOBAL
+// template ids, ordered that way and fed to the same std::sort + std::unique as Detector::match (:1143-1145).
+// class_order == NULL: every class slot once, ascending (the "all classes" request).
+int mergeRecords(const sbm_device_rec *recs, const int *n_per_rank, int n_ranks, const int *class_sizes, int n_classes, int mode,
+                 const int *class_order, int n_order, bool finalize, std::vector<sbm_match_rec> &m)
+{
+    struct G
+    {
+        int32_t tid;
+        uint32_t key;
+        const sbm_device_rec *r;
+    };
+    std::vector<std::vector<G>> per_class(n_classes);
+    size_t at = 0;
+    for (int rk = 0; rk < n_ranks; ++rk)
+    {
+        const int *cs = class_sizes + (size_t)rk * n_classes;
+        std::vector<uint32_t> begin(n_classes + 1, 0);
+        for (int k = 0; k < n_classes; ++k)
+        {
+            if (cs[k] < 0)
+                return fail(SBM_ERR_BAD_ARG, "negative class size");
+            begin[k + 1] = begin[k] + (uint32_t)cs[k];
+        }
+        if (n_per_rank[rk] < 0 || (n_per_rank[rk] > 0 && !recs))
+            return fail(SBM_ERR_BAD_ARG, "bad record count of rank %d", rk);
+        for (int i = 0; i < n_per_rank[rk]; ++i, ++at)
+        {
+            const sbm_device_rec &r = recs[at];
+            if (r.template_gid >= begin[n_classes])
+                return fail(SBM_ERR_BAD_ARG, "rank %d record %d names local template %u of %u", rk, i, r.template_gid, begin[n_classes]);
+            const int k = (int)(std::upper_bound(begin.begin(), begin.end(), r.template_gid) - begin.begin()) - 1;
+            const int local = (int)(r.template_gid - begin[k]);
+            int tid;
+            if (mode == SBM_SHARD_INTERLEAVED)
+                tid = rk + local * n_ranks; // rank rk owns ids rk, rk + G, rk + 2G, ...
+            else
+            {
+                tid = local; // rank rk owns a contiguous block after the blocks of the lower ranks
+                for (int q = 0; q < rk; ++q)
+                    tid += class_sizes[(size_t)q * n_classes + k];
+            }
+            per_class[k].push_back(G{tid, r.order_key, &r});
+        }
+    }
+    for (auto &v : per_class)
+        std::sort(v.begin(), v.end(), [](const G &a, const G &b) { return a.tid != b.tid ? a.tid < b.tid : a.key < b.key; });
+    m.clear();
+    m.reserve(at);
+    std::vector<int> all;
+    if (!class_order || n_order <= 0)
+    {
+        for (int k = 0; k < n_classes; ++k)
+            all.push_back(k);
+        class_order = all.data(), n_order = n_classes;
+    }
+    for (int i = 0; i < n_order; ++i)
+    {
+        const int k = class_order[i];
+        if (k < 0 || k >= n_classes) // unknown ids are skipped (:1136-1138)
+            continue;
+        for (const G &e : per_class[k])
+            m.push_back(sbm_match_rec{e.r->x, e.r->y, e.r->similarity, k, e.tid});
+    }
+    if (finalize)
+    {
+        std::sort(m.begin(), m.end(), [](const sbm_match_rec &a, const sbm_match_rec &b) {
+            if (a.similarity != b.similarity)
+                return a.similarity > b.similarity;
+            return a.template_id < b.template_id;
+        });
+        m.erase(std::unique(m.begin(), m.end(),
+                            [](const sbm_match_rec &a, const sbm_match_rec &b) {
+                                return a.x == b.x && a.y == b.y && a.similarity == b.similarity && a.class_idx == b.class_idx;
+                            }),
+                m.end());
+    }
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Multi-GPU group: result blocks and the one exchange.
+// A frame's result travels as one block: {uint32 count, uint32 overflow, uint32 0, uint32 0} + cap records of 20 bytes.
+// Every rank fills one block per frame (k_export writes the header and the records), then ONE ncclAllGather moves all
+// blocks of all ranks -- counts and records in the same buffer, no second collective.
+// ------------------------------------------------------------------------------------------------
+void destroyGroup(sbm_ctx *c)
+{
+    sbm_ctx::Group &G = c->group;
+    if (!G.on)
+        return;
+    cudaSetDevice(c->device);
+    cudaDeviceSynchronize();
+    if (G.comm)
+        if (NcclApi *N = NcclApi::get())
+            N->CommDestroy(G.comm);
+    freeDev(G.d_send);
+    freeDev(G.d_recv);
+    if (G.h_recv)
+        cudaFreeHost(G.h_recv);
+    if (G.mode != SBM_GROUP_FRAMES) // the context holds a slice of every class: meaningless without the group
+    {
+        c->classes.clear();
+        c->templates_dirty = true;
+    }
+    G = sbm_ctx::Group();
+}
+
+constexpr size_t GROUP_HEAD = 16;
+size_t groupBlockBytes(uint32_t cap) { return GROUP_HEAD + (size_t)cap * sizeof(Cand); }
+
+int ncclFail(NcclApi *N, int r, const char *what) { return fail(SBM_ERR_CUDA, "%s failed: %s", what, N->GetErrorString(r)); }
+
+int ensureGroupBuffers(sbm_ctx *c, size_t send_bytes, bool own_recv)
+{
+    sbm_ctx::Group &G = c->group;
+    if (G.send_alloc < send_bytes)
+    {
+        CK(cudaDeviceSynchronize());
+        freeDev(G.d_send);
+        CK(cudaMalloc(&G.d_send, send_bytes));
+        G.send_alloc = send_bytes;
+    }
+    const size_t recv_bytes = send_bytes * G.n;
+    if (own_recv && G.recv_alloc < recv_bytes)
+    {
+        CK(cudaDeviceSynchronize());
+        freeDev(G.d_recv);
+        CK(cudaMalloc(&G.d_recv, recv_bytes));
+        G.recv_alloc = recv_bytes;
+    }
+    if (own_recv && G.h_alloc < recv_bytes)
+    {
+        if (G.h_recv)
+            cudaFreeHost(G.h_recv);
+        G.h_recv = nullptr;
+        CK(cudaMallocHost(&G.h_recv, recv_bytes));
+        G.h_alloc = recv_bytes;
+    }
+    return 0;
+}
+
+// Enqueue n_frames frames (host pointers `imgs`, or resident at d_imgs + i * frame_stride) over the frame slots with their
+// results exported into the send blocks, join the slot streams on `user`, and allgather the blocks into d_gathered on `user`.
+int groupEnqueue(sbm_ctx *c, const uint8_t *const *imgs, const uint8_t *const *masks, const void *d_imgs, size_t frame_stride, int n_frames,
+                 int w, int h, int ch, size_t stride, float threshold, const int *class_idx, int n_classes, uint32_t cap, uint8_t *d_gathered,
+                 cudaStream_t user)
+{
+    sbm_ctx::Group &G = c->group;
+    NcclApi *N = NcclApi::get();
+    if (!G.on || !N)
+        return fail(SBM_ERR_STATE, "no group: call sbm_group_create first");
+    int rc;
+    const int NS = frameSlots();
+    const int ns = std::min(n_frames, NS);
+    for (int k = 0; k < ns; ++k)
+        if ((rc = prepare(c, c->slot[k], w, h, ch, class_idx, n_classes)))
+            return rc;
+    const size_t blk = groupBlockBytes(cap);
+    if ((rc = ensureGroupBuffers(c, blk * n_frames, d_gathered == nullptr)))
+        return rc;
+    if (!d_gathered)
+        d_gathered = G.d_recv;
+    Slot &s0 = c->slot[0];
+    if (ns > 0)
+    {
+        CK(cudaEventRecord(s0.ev[0], user));
+        for (int k = 0; k < ns; ++k)
+            CK(cudaStreamWaitEvent(c->slot[k].stream, s0.ev[0], 0));
+    }
+    const bool timing = c->timing, debug = c->debug;
+    c->timing = false, c->debug = false;
+    rc = 0;
+    for (int i = 0; i < n_frames && !rc; ++i)
+    {
+        Slot &s = c->slot[i % NS];
+        uint8_t *block = G.d_send + (size_t)i * blk;
+        const uint8_t *img = nullptr, *dm = nullptr;
+        if (imgs)
+        {
+            if ((rc = uploadFrame(s, imgs[i], w, h, ch, stride, masks ? masks[i] : nullptr, &dm)))
+                break;
+            img = s.d_frame;
+        }
+        else
+            img = (const uint8_t *)d_imgs + (size_t)i * frame_stride;
+        if (dm) // masks take the eager path, straight into the block
+            rc = enqueueFrame(c, s, img, dm, threshold, s.stream, (Cand *)(block + GROUP_HEAD), cap, (uint32_t *)block);
+        else if (!(rc = launchFrameGraph(c, s, img, threshold, false, s.stream)))
+            rc = exportResults(c, s, s.stream, block + GROUP_HEAD, cap, block);
+    }
+    c->timing = timing, c->debug = debug;
+    if (rc)
+        return rc;
+    for (int k = 0; k < ns; ++k)
+    {
+        CK(cudaEventRecord(c->slot[k].ev[1], c->slot[k].stream));
+        CK(cudaStreamWaitEvent(user, c->slot[k].ev[1], 0));
+    }
+    if (n_frames > 0)
+    {
+        const int r = N->AllGather(G.d_send, d_gathered, blk * n_frames, NcclApi::kUint8, G.comm, user);
+        if (r)
+            return ncclFail(N, r, "ncclAllGather");
+    }
+    return 0;
+}
+
+// gathered host blocks -> final lists.  Template modes: frame f's list = merge of the n ranks' blocks of frame f (n_frames
+// lists).  Frame mode: every (rank, frame) block is a complete list of its own frame (n * n_frames lists, rank-major).
+// *worst = largest record count any block reported, *overflow = a stage or block overflowed somewhere.
+int groupFinalize(sbm_ctx *c, const uint8_t *h, int n_frames, uint32_t cap, const int *class_idx, int n_classes, bool finalize,
+                  sbm_match_rec *out, int out_cap, int *frame_begin, uint32_t *worst, bool *overflow)
+{
+    sbm_ctx::Group &G = c->group;
+    const size_t blk = groupBlockBytes(cap);
+    *worst = 0, *overflow = false;
+    for (int r = 0; r < G.n; ++r)
+        for (int f = 0; f < n_frames; ++f)
+        {
+            const uint32_t *hd = (const uint32_t *)(h + ((size_t)r * n_frames + f) * blk);
+            *worst = std::max(*worst, hd[0]);
+            if (hd[1] || hd[0] > cap)
+                *overflow = true;
+        }
+    if (*overflow)
+        return 0;
+    int used = 0;
+    bool full = false;
+    frame_begin[0] = 0;
+    std::vector<sbm_match_rec> m;
+    if (G.mode == SBM_GROUP_FRAMES)
+    {
+        for (int r = 0; r < G.n; ++r)
+            for (int f = 0; f < n_frames; ++f)
+            {
+                const uint8_t *b = h + ((size_t)r * n_frames + f) * blk;
+                const uint32_t n = *(const uint32_t *)b;
+                int got = 0;
+                const int room = full ? 0 : std::max(0, out_cap - used);
+                int rc = orderRecords(c, (const Cand *)(b + GROUP_HEAD), n, finalize, out ? out + used : nullptr, room, &got);
+                if (rc == SBM_ERR_CAPACITY)
+                    full = true, rc = 0;
+                if (rc)
+                    return rc;
+                used += got;
+                frame_begin[r * n_frames + f + 1] = used;
+            }
+    }
+    else
+    {
+        const int n_slots = (int)c->classes.size();
+        std::vector<int> sizes((size_t)G.n * std::max(1, n_slots), 0);
+        for (int r = 0; r < G.n; ++r)
+            for (int k = 0; k < n_slots; ++k)
+                sizes[(size_t)r * n_slots + k] = shardCount((size_t)k < G.global_n.size() ? G.global_n[k] : 0, r, G.n, G.mode);
+        // the caller's class order against the GLOBAL class sizes (a rank whose slice of a class is empty must still
+        // produce the same merged list as the others)
+        std::vector<int> order;
+        if (!class_idx || n_classes <= 0)
+        {
+            for (int k = 0; k < n_slots; ++k)
+                if ((size_t)k < G.global_n.size() && G.global_n[k] > 0)
+                    order.push_back(k);
+        }
+        else
+            for (int i = 0; i < n_classes; ++i)
+                if (class_idx[i] >= 0 && (size_t)class_idx[i] < G.global_n.size() && G.global_n[class_idx[i]] > 0)
+                    order.push_back(class_idx[i]);
+        std::vector<sbm_device_rec> recs;
+        std::vector<int> per_rank(G.n);
+        for (int f = 0; f < n_frames; ++f)
+        {
+            recs.clear();
+            for (int r = 0; r < G.n; ++r)
+            {
+                const uint8_t *b = h + ((size_t)r * n_frames + f) * blk;
+                const uint32_t n = *(const uint32_t *)b;
+                per_rank[r] = (int)n;
+                const sbm_device_rec *p = (const sbm_device_rec *)(b + GROUP_HEAD);
+                recs.insert(recs.end(), p, p + n);
+            }
+            int rc = 0;
+            m.clear();
+            if (n_slots > 0 && !order.empty())
+                rc = mergeRecords(recs.data(), per_rank.data(), G.n, sizes.data(), n_slots, G.mode, order.data(), (int)order.size(), finalize, m);
+            if (rc)
+                return rc;
+            if (!full && used + (int)m.size() <= out_cap)
+            {
+                if (!m.empty() && out)
+                    memcpy(out + used, m.data(), m.size() * sizeof(sbm_match_rec));
+            }
+            else
+                full = true;
+            used += (int)m.size();
+            frame_begin[f + 1] = used;
+        }
+    }
+    if (full)
+        return fail(SBM_ERR_CAPACITY, "output holds %d matches, %d needed", out_cap, used);
+    return 0;
+}
+
+// host frames -> final host lists through the group (see sbm_group_match_batch)
+int groupMatchHost(sbm_ctx *c, const uint8_t *const *imgs, const uint8_t *const *masks, int n_frames, int w, int h, int ch, size_t stride,
+                   float threshold, const int *class_idx, int n_classes, bool finalize, sbm_match_rec *out, int cap, int *frame_begin)
+{
+    sbm_ctx::Group &G = c->group;
+    int rc;
+    for (int attempt = 0; attempt < 8; ++attempt)
+    {
+        if ((rc = ensureStream(c->slot[0])))
+            return rc;
+        cudaStream_t st = c->slot[0].stream;
+        if ((rc = groupEnqueue(c, imgs, masks, nullptr, 0, n_frames, w, h, ch, stride, threshold, class_idx, n_classes, G.cap, nullptr, st)))
+            return rc;
+        const size_t bytes = groupBlockBytes(G.cap) * n_frames * G.n;
+        CK(cudaMemcpyAsync(G.h_recv, G.d_recv, bytes, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        uint32_t worst = 0;
+        bool overflow = false;
+        if ((rc = groupFinalize(c, G.h_recv, n_frames, G.cap, class_idx, n_classes, finalize, out, cap, frame_begin, &worst, &overflow)))
+            return rc;
+        if (!overflow)
+            return 0;
+        // every rank sees the same gathered headers, so every rank takes the same decision: larger blocks, larger stage
+        // buffers, and the whole batch again (the collective stays matched across the ranks)
+        uint32_t nc = G.cap;
+        while (nc < worst || nc == G.cap)
+            nc *= 2;
+        G.cap = nc;
+        CK(cudaDeviceSynchronize());
+        for (Slot &s : c->slot)
+            if (s.cap < 4 * nc || s.cap < (1u << 18))
+            {
+                freeDev(s.d_buf[0]);
+                freeDev(s.d_buf[1]);
+                s.cap = std::max(4 * nc, 1u << 18);
+                s.graph_epoch = 0;
+            }
+    }
+    return fail(SBM_ERR_CAPACITY, "group result blocks keep overflowing");
+}
 } // namespace
 
 extern "C"
@@ -1199,6 +1578,10 @@ int sbm_create(const int *T, int levels, float weak, float strong, int num_featu
     CK(cudaSetDevice(device));
     sbm_ctx *c = new sbm_ctx();
     c->device = device;
+    if (cudaDeviceGetAttribute(&c->sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || c->sms < 1)
+        c->sms = 148;
+    c->refine_grid[0] = computeRefineGrid(c->sms, false);
+    c->refine_grid[1] = computeRefineGrid(c->sms, true);
     c->T.assign(T, T + levels);
     c->levels = levels;
     c->weak = weak, c->strong = strong, c->num_features = num_features;
@@ -1213,6 +1596,7 @@ int sbm_destroy(sbm_ctx *c)
         return 0;
     cudaSetDevice(c->device);
     cudaDeviceSynchronize();
+    destroyGroup(c);
     for (auto &s : c->slot)
         destroySlot(s);
     for (auto &l : c->tl)
@@ -1244,9 +1628,38 @@ int sbm_set_class_templates(sbm_ctx *c, int class_idx, int n_templates, const sb
     if ((size_t)class_idx >= c->classes.size())
         c->classes.resize(class_idx + 1);
     ClassSet &cs = c->classes[class_idx];
-    cs.n = n_templates;
-    cs.desc.assign(desc, desc + nd);
-    cs.feats.assign(feats, feats + nf);
+    sbm_ctx::Group &G = c->group;
+    if (G.on && G.mode != SBM_GROUP_FRAMES)
+    {
+        // template sharding: the caller hands every rank the FULL class, this rank keeps its slice (ids rank, rank + n,
+        // ... or its contiguous block) and remembers the size of the whole class for the merge after the allgather
+        if ((size_t)class_idx >= G.global_n.size())
+            G.global_n.resize(class_idx + 1, 0);
+        G.global_n[class_idx] = n_templates;
+        cs.n = 0;
+        cs.desc.clear();
+        cs.feats.clear();
+        size_t fo = 0;
+        for (int t = 0; t < n_templates; ++t)
+        {
+            size_t tf = 0;
+            for (int l = 0; l < c->levels; ++l)
+                tf += desc[(size_t)t * c->levels + l].num_features;
+            if (shardOwns(t, n_templates, G.rank, G.n, G.mode))
+            {
+                cs.desc.insert(cs.desc.end(), desc + (size_t)t * c->levels, desc + (size_t)(t + 1) * c->levels);
+                cs.feats.insert(cs.feats.end(), feats + fo, feats + fo + tf);
+                ++cs.n;
+            }
+            fo += tf;
+        }
+    }
+    else
+    {
+        cs.n = n_templates;
+        cs.desc.assign(desc, desc + nd);
+        cs.feats.assign(feats, feats + nf);
+    }
     c->templates_dirty = true;
     return 0;
 }
@@ -1257,7 +1670,28 @@ int sbm_clear_templates(sbm_ctx *c)
         return fail(SBM_ERR_BAD_ARG, "null context");
     std::lock_guard<std::mutex> lock(c->mu);
     c->classes.clear();
+    c->group.global_n.clear();
     c->templates_dirty = true;
+    return 0;
+}
+
+int sbm_set_candidate_capacity(sbm_ctx *c, int cap)
+{
+    if (!c || cap < 1)
+        return fail(SBM_ERR_BAD_ARG, "sbm_set_candidate_capacity: bad arguments");
+    std::lock_guard<std::mutex> lock(c->mu);
+    CK(cudaSetDevice(c->device));
+    CK(cudaDeviceSynchronize()); // frames in flight still write the old buffers
+    const uint32_t want = std::max<uint32_t>(1024u, (uint32_t)cap);
+    for (Slot &s : c->slot)
+    {
+        if (s.cap == want)
+            continue;
+        freeDev(s.d_buf[0]);
+        freeDev(s.d_buf[1]);
+        s.cap = want;
+        s.graph_epoch = 0; // the capacities are baked into the slot's graph
+    }
     return 0;
 }
 
@@ -1336,6 +1770,8 @@ int sbm_match_device(sbm_ctx *c, const void *d_img, int w, int h, int ch, const 
 {
     if (!c || !d_img)
         return fail(SBM_ERR_BAD_ARG, "null argument");
+    if (!d_records != !d_count)
+        return fail(SBM_ERR_BAD_ARG, "d_records and d_count must be given together");
     std::lock_guard<std::mutex> lock(c->mu);
     CK(cudaSetDevice(c->device));
     Slot &s = c->slot[0];
@@ -1349,7 +1785,7 @@ int sbm_match_device(sbm_ctx *c, const void *d_img, int w, int h, int ch, const 
                             d_records ? (uint32_t)cap : 0, (uint32_t *)d_count);
     if ((rc = launchFrameGraph(c, s, (const uint8_t *)d_img, threshold, false, st)))
         return rc;
-    return exportResults(s, st, d_records, (uint32_t)cap, d_count);
+    return exportResults(c, s, st, d_records, (uint32_t)cap, d_count);
 }
 
 int sbm_match_batch_device(sbm_ctx *c, const void *d_imgs, size_t frame_stride, int n_frames, int w, int h, int ch, float threshold,
@@ -1381,7 +1817,7 @@ int sbm_match_batch_device(sbm_ctx *c, const void *d_imgs, size_t frame_stride, 
         Slot &s = c->slot[i % NS];
         const uint8_t *img = (const uint8_t *)d_imgs + (size_t)i * frame_stride;
         if ((rc = launchFrameGraph(c, s, img, threshold, false, s.stream)) ||
-            (rc = exportResults(s, s.stream, (Cand *)d_records + (size_t)i * cap_per_frame, (uint32_t)cap_per_frame,
+            (rc = exportResults(c, s, s.stream, (Cand *)d_records + (size_t)i * cap_per_frame, (uint32_t)cap_per_frame,
                                 (uint32_t *)d_counts + 2 * (size_t)i)))
         {
             c->timing = timing, c->debug = debug;
@@ -1430,78 +1866,159 @@ int sbm_finalize_records(sbm_ctx *c, const sbm_device_rec *recs, int n, const in
 // :1170, :1200-1216), so the ranks' records are re-labelled with GLOBAL template ids, ordered that way and fed
 // to the same std::sort + std::unique as Detector::match (:1143-1145).
 int sbm_merge_shard_records(const sbm_device_rec *recs, const int *n_per_rank, int n_ranks, const int *class_sizes, int n_classes,
-                            int mode, int finalize, sbm_match_rec *out, int cap, int *n_out)
+                            int mode, const int *class_order, int n_order, int finalize, sbm_match_rec *out, int cap, int *n_out)
 {
     if (!n_per_rank || !class_sizes || !n_out || n_ranks < 1 || n_classes < 1 || (mode != SBM_SHARD_INTERLEAVED && mode != SBM_SHARD_CONTIGUOUS))
         return fail(SBM_ERR_BAD_ARG, "sbm_merge_shard_records: bad arguments");
-    struct G
-    {
-        int32_t cls, tid;
-        uint32_t key;
-        const sbm_device_rec *r;
-    };
-    std::vector<G> g;
-    size_t at = 0;
-    for (int rk = 0; rk < n_ranks; ++rk)
-    {
-        const int *cs = class_sizes + (size_t)rk * n_classes;
-        std::vector<uint32_t> begin(n_classes + 1, 0);
-        for (int k = 0; k < n_classes; ++k)
-        {
-            if (cs[k] < 0)
-                return fail(SBM_ERR_BAD_ARG, "negative class size");
-            begin[k + 1] = begin[k] + (uint32_t)cs[k];
-        }
-        if (n_per_rank[rk] < 0 || (n_per_rank[rk] > 0 && !recs))
-            return fail(SBM_ERR_BAD_ARG, "bad record count of rank %d", rk);
-        for (int i = 0; i < n_per_rank[rk]; ++i, ++at)
-        {
-            const sbm_device_rec &r = recs[at];
-            if (r.template_gid >= begin[n_classes])
-                return fail(SBM_ERR_BAD_ARG, "rank %d record %d names local template %u of %u", rk, i, r.template_gid, begin[n_classes]);
-            const int k = (int)(std::upper_bound(begin.begin(), begin.end(), r.template_gid) - begin.begin()) - 1;
-            const int local = (int)(r.template_gid - begin[k]);
-            int tid;
-            if (mode == SBM_SHARD_INTERLEAVED)
-                tid = rk + local * n_ranks; // rank rk owns ids rk, rk + G, rk + 2G, ...
-            else
-            {
-                tid = local; // rank rk owns a contiguous block after the blocks of the lower ranks
-                for (int q = 0; q < rk; ++q)
-                    tid += class_sizes[(size_t)q * n_classes + k];
-            }
-            g.push_back(G{k, tid, r.order_key, &r});
-        }
-    }
-    std::sort(g.begin(), g.end(), [](const G &a, const G &b) {
-        if (a.cls != b.cls)
-            return a.cls < b.cls;
-        if (a.tid != b.tid)
-            return a.tid < b.tid;
-        return a.key < b.key;
-    });
     std::vector<sbm_match_rec> m;
-    m.reserve(g.size());
-    for (const G &e : g)
-        m.push_back(sbm_match_rec{e.r->x, e.r->y, e.r->similarity, e.cls, e.tid});
-    if (finalize)
-    {
-        std::sort(m.begin(), m.end(), [](const sbm_match_rec &a, const sbm_match_rec &b) {
-            if (a.similarity != b.similarity)
-                return a.similarity > b.similarity;
-            return a.template_id < b.template_id;
-        });
-        m.erase(std::unique(m.begin(), m.end(),
-                            [](const sbm_match_rec &a, const sbm_match_rec &b) {
-                                return a.x == b.x && a.y == b.y && a.similarity == b.similarity && a.class_idx == b.class_idx;
-                            }),
-                m.end());
-    }
+    int rc = mergeRecords(recs, n_per_rank, n_ranks, class_sizes, n_classes, mode, class_order, n_order, finalize != 0, m);
+    if (rc)
+        return rc;
     *n_out = (int)m.size();
     if ((int)m.size() > cap)
         return fail(SBM_ERR_CAPACITY, "output holds %d matches, %zu needed", cap, m.size());
     if (!m.empty() && out)
         memcpy(out, m.data(), m.size() * sizeof(sbm_match_rec));
+    return 0;
+}
+
+// ---------------------------------------------------------------- multi-GPU group
+
+int sbm_group_unique_id(void *id128)
+{
+    if (!id128)
+        return fail(SBM_ERR_BAD_ARG, "null argument");
+    NcclApi *N = NcclApi::get();
+    if (!N)
+        return fail(SBM_ERR_STATE, "%s", NcclApi::loadError().c_str());
+    NcclApi::unique_id id;
+    const int r = N->GetUniqueId(&id);
+    if (r)
+        return ncclFail(N, r, "ncclGetUniqueId");
+    memcpy(id128, &id, sizeof(id));
+    return 0;
+}
+
+int sbm_group_create(sbm_ctx *c, int n_ranks, int rank, const void *id128, int mode)
+{
+    if (!c || !id128 || n_ranks < 1 || rank < 0 || rank >= n_ranks ||
+        (mode != SBM_GROUP_TEMPLATES && mode != SBM_GROUP_TEMPLATES_CONTIGUOUS && mode != SBM_GROUP_FRAMES))
+        return fail(SBM_ERR_BAD_ARG, "sbm_group_create: bad arguments");
+    NcclApi *N = NcclApi::get();
+    if (!N)
+        return fail(SBM_ERR_STATE, "%s", NcclApi::loadError().c_str());
+    std::lock_guard<std::mutex> lock(c->mu);
+    if (c->group.on)
+        return fail(SBM_ERR_STATE, "the context already belongs to a group");
+    for (const ClassSet &cs : c->classes)
+        if (cs.n > 0 && mode != SBM_GROUP_FRAMES)
+            return fail(SBM_ERR_STATE, "template sharding: create the group before installing templates (every rank is then handed the full classes)");
+    CK(cudaSetDevice(c->device));
+    NcclApi::unique_id id;
+    memcpy(&id, id128, sizeof(id));
+    NcclApi::comm_t comm = nullptr;
+    const int r = N->CommInitRank(&comm, n_ranks, id, rank); // collective: returns once every rank has called it
+    if (r)
+        return ncclFail(N, r, "ncclCommInitRank");
+    c->group.on = true;
+    c->group.n = n_ranks, c->group.rank = rank, c->group.mode = mode;
+    c->group.comm = comm;
+    c->group.global_n.clear();
+    return 0;
+}
+
+int sbm_group_destroy(sbm_ctx *c)
+{
+    if (!c)
+        return 0;
+    std::lock_guard<std::mutex> lock(c->mu);
+    destroyGroup(c);
+    return 0;
+}
+
+int sbm_group_info(sbm_ctx *c, int *n_ranks, int *rank, int *mode)
+{
+    if (!c)
+        return fail(SBM_ERR_BAD_ARG, "null context");
+    if (n_ranks)
+        *n_ranks = c->group.on ? c->group.n : 1;
+    if (rank)
+        *rank = c->group.on ? c->group.rank : 0;
+    if (mode)
+        *mode = c->group.on ? c->group.mode : -1;
+    return c->group.on ? 1 : 0;
+}
+
+int sbm_group_match_batch(sbm_ctx *c, const uint8_t *const *imgs, const uint8_t *const *masks, int n_frames, int w, int h, int ch, size_t stride,
+                          float threshold, const int *class_idx, int n_classes, sbm_match_rec *out, int cap, int *frame_begin)
+{
+    if (!c || !imgs || n_frames < 0 || !frame_begin)
+        return fail(SBM_ERR_BAD_ARG, "null argument");
+    for (int i = 0; i < n_frames; ++i)
+        if (!imgs[i])
+            return fail(SBM_ERR_BAD_ARG, "frame %d is null", i);
+    std::lock_guard<std::mutex> lock(c->mu);
+    CK(cudaSetDevice(c->device));
+    if (!c->group.on)
+        return fail(SBM_ERR_STATE, "no group: call sbm_group_create first");
+    return groupMatchHost(c, imgs, masks, n_frames, w, h, ch, stride, threshold, class_idx, n_classes, true, out, cap, frame_begin);
+}
+
+int sbm_group_match(sbm_ctx *c, const uint8_t *img, int w, int h, int ch, size_t stride, const uint8_t *mask, float threshold,
+                    const int *class_idx, int n_classes, sbm_match_rec *out, int cap, int *n_out)
+{
+    if (!c || !img || !n_out)
+        return fail(SBM_ERR_BAD_ARG, "null argument");
+    std::lock_guard<std::mutex> lock(c->mu);
+    CK(cudaSetDevice(c->device));
+    if (!c->group.on || c->group.mode == SBM_GROUP_FRAMES)
+        return fail(SBM_ERR_STATE, "sbm_group_match needs a template-sharding group (frame sharding: sbm_group_match_batch)");
+    int begin[2] = {0, 0};
+    const uint8_t *imgs[1] = {img}, *masks[1] = {mask};
+    const int rc = groupMatchHost(c, imgs, mask ? masks : nullptr, 1, w, h, ch, stride, threshold, class_idx, n_classes, true, out, cap, begin);
+    *n_out = begin[1];
+    return rc;
+}
+
+size_t sbm_group_block_bytes(int cap_per_frame) { return cap_per_frame > 0 ? groupBlockBytes((uint32_t)cap_per_frame) : 0; }
+
+int sbm_group_match_batch_device(sbm_ctx *c, const void *d_imgs, size_t frame_stride, int n_frames, int w, int h, int ch, float threshold,
+                                 const int *class_idx, int n_classes, void *d_gathered, int cap_per_frame, void *stream)
+{
+    if (!c || !d_imgs || n_frames < 0 || !d_gathered || cap_per_frame <= 0)
+        return fail(SBM_ERR_BAD_ARG, "bad argument");
+    std::lock_guard<std::mutex> lock(c->mu);
+    CK(cudaSetDevice(c->device));
+    if (!c->group.on)
+        return fail(SBM_ERR_STATE, "no group: call sbm_group_create first");
+    return groupEnqueue(c, nullptr, nullptr, d_imgs, frame_stride, n_frames, w, h, ch, 0, threshold, class_idx, n_classes, (uint32_t)cap_per_frame,
+                        (uint8_t *)d_gathered, (cudaStream_t)stream);
+}
+
+int sbm_group_finalize(sbm_ctx *c, const void *h_gathered, int n_frames, int cap_per_frame, const int *class_idx, int n_classes, int finalize,
+                       sbm_match_rec *out, int cap, int *frame_begin)
+{
+    if (!c || !h_gathered || n_frames < 0 || cap_per_frame <= 0 || !frame_begin)
+        return fail(SBM_ERR_BAD_ARG, "bad argument");
+    std::lock_guard<std::mutex> lock(c->mu);
+    CK(cudaSetDevice(c->device));
+    if (!c->group.on)
+        return fail(SBM_ERR_STATE, "no group: call sbm_group_create first");
+    int rc;
+    if ((rc = ensureTemplates(c)) || (rc = ensureActive(c, class_idx, n_classes)))
+        return rc;
+    uint32_t worst = 0;
+    bool overflow = false;
+    if ((rc = groupFinalize(c, (const uint8_t *)h_gathered, n_frames, (uint32_t)cap_per_frame, class_idx, n_classes, finalize != 0, out, cap,
+                            frame_begin, &worst, &overflow)))
+        return rc;
+    if (overflow)
+    {
+        const int lists = c->group.mode == SBM_GROUP_FRAMES ? c->group.n * n_frames : n_frames;
+        frame_begin[lists] = (int)worst;
+        return fail(SBM_ERR_CAPACITY, "a result block overflowed (largest count %u, cap_per_frame %d) or a stage exceeded the candidate capacity", worst,
+                    cap_per_frame);
+    }
     return 0;
 }
 
@@ -1816,7 +2333,7 @@ int sbm_time_kernels(sbm_ctx *c, float threshold, int iters, float *ms, int n_ms
             src = LB.d_src;
         }
         const uint8_t *nm = nullptr;
-        SBM_TIME(3 * l + 1, (void)launchOrient(c->c, src, G.w, G.h, nm, l, c->w, weak_sq, LB.d_quant, st));
+        SBM_TIME(3 * l + 1, (void)launchOrient(c->sms, c->c, src, G.w, G.h, nm, l, c->w, weak_sq, LB.d_quant, st));
         uint8_t *nd = nullptr;
         SBM_TIME(3 * l + 2, (void)launchSpread(G, LB.d_quant, LB.d_lm, nd, nd, st));
     }
@@ -1835,7 +2352,7 @@ int sbm_time_kernels(sbm_ctx *c, float threshold, int iters, float *ms, int n_ms
     {
         const LevelGeom &G = c->geom[l];
         if (stage == 1)
-            SBM_TIME(3 * L + stage, (void)launchRefine(G.tiled, refineGrid(G.tiled), s.lv[l].d_lm, c->tl[l].d_tl, c->tl[l].d_feats, s.d_buf[0],
+            SBM_TIME(3 * L + stage, (void)launchRefine(G.tiled, refineGrid(c, G.tiled), s.lv[l].d_lm, c->tl[l].d_tl, c->tl[l].d_feats, s.d_buf[0],
                                                        s.d_counts + 0, s.cap, s.d_buf[1], d_tmp + 1, 0u, G.w, G.h, G.T, threshold, nullptr, 0,
                                                        reinterpret_cast<unsigned long long *>(d_tmp + 10), st));
     }
@@ -1875,49 +2392,55 @@ int sbm_quantized_orientations(sbm_ctx *c, const uint8_t *img, int w, int h, int
         return rc_s;
     cudaStream_t st = s.stream;
     const size_t row = (size_t)w * ch;
-    uint8_t *d_a = nullptr, *d_b = nullptr, *d_q = nullptr;
-    float *d_mag = nullptr, *d_ang = nullptr;
-    CK(cudaMalloc(&d_a, row * h));
+    // every early return (CK) releases what was allocated so far
+    struct DevBuf
+    {
+        void *p = nullptr;
+        ~DevBuf() { cudaFree(p); }
+        void swap(DevBuf &o) { std::swap(p, o.p); }
+    } a, b, q, mag, ang;
+    CK(cudaMalloc(&a.p, row * h));
     if (stride == 0 || stride == row)
-        CK(cudaMemcpyAsync(d_a, img, row * h, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(a.p, img, row * h, cudaMemcpyHostToDevice, st));
     else
-        CK(cudaMemcpy2DAsync(d_a, row, img, stride, row, h, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpy2DAsync(a.p, row, img, stride, row, h, cudaMemcpyHostToDevice, st));
     int lw = w, lh = h;
     for (int l = 1; l <= level; ++l) // cv::pyrDown(src, src, Size(cols/2, rows/2))  line2Dup.cpp:431-433
     {
         const int dw = lw / 2, dh = lh / 2;
-        CK(cudaMalloc(&d_b, (size_t)dw * dh * ch));
+        DevBuf next;
+        CK(cudaMalloc(&next.p, (size_t)dw * dh * ch));
         dim3 g((dw + 31) / 32, (dh + K1B_ROWS - 1) / K1B_ROWS);
         if (ch == 3)
-            k_pyrdown<3><<<g, K1B_THREADS, 0, st>>>(d_a, lw, lh, d_b, dw, dh);
+            k_pyrdown<3><<<g, K1B_THREADS, 0, st>>>((const uint8_t *)a.p, lw, lh, (uint8_t *)next.p, dw, dh);
         else
-            k_pyrdown<1><<<g, K1B_THREADS, 0, st>>>(d_a, lw, lh, d_b, dw, dh);
-        CK(cudaStreamSynchronize(st));
-        cudaFree(d_a);
-        d_a = d_b, d_b = nullptr;
+            k_pyrdown<1><<<g, K1B_THREADS, 0, st>>>((const uint8_t *)a.p, lw, lh, (uint8_t *)next.p, dw, dh);
+        CK(cudaStreamSynchronize(st)); // the previous level is freed when `next` leaves the scope
+        a.swap(next);
         lw = dw, lh = dh;
     }
     const size_t px = (size_t)lw * lh;
-    CK(cudaMalloc(&d_q, px));
-    CK(cudaMalloc(&d_mag, px * sizeof(float)));
-    CK(cudaMalloc(&d_ang, px * sizeof(float)));
+    CK(cudaMalloc(&q.p, px));
+    CK(cudaMalloc(&mag.p, px * sizeof(float)));
+    CK(cudaMalloc(&ang.p, px * sizeof(float)));
     dim3 g1((lw + K1_TW - 1) / K1_TW, (lh + 15) / 16);
     const float weak_sq = c->weak * c->weak;
     if (ch == 3)
-        k_orient<3, 16, true><<<g1, K1_THREADS, 0, st>>>(d_a, lw, lh, nullptr, 0, lw, weak_sq, d_q, d_mag, d_ang);
+        k_orient<3, 16, true><<<g1, K1_THREADS, 0, st>>>((const uint8_t *)a.p, lw, lh, nullptr, 0, lw, weak_sq, (uint8_t *)q.p, (float *)mag.p,
+                                                          (float *)ang.p);
     else
-        k_orient<1, 16, true><<<g1, K1_THREADS, 0, st>>>(d_a, lw, lh, nullptr, 0, lw, weak_sq, d_q, d_mag, d_ang);
+        k_orient<1, 16, true><<<g1, K1_THREADS, 0, st>>>((const uint8_t *)a.p, lw, lh, nullptr, 0, lw, weak_sq, (uint8_t *)q.p, (float *)mag.p,
+                                                          (float *)ang.p);
     CK(cudaGetLastError());
     if (magnitude)
-        CK(cudaMemcpyAsync(magnitude, d_mag, px * sizeof(float), cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(magnitude, mag.p, px * sizeof(float), cudaMemcpyDeviceToHost, st));
     if (angle_ori)
-        CK(cudaMemcpyAsync(angle_ori, d_ang, px * sizeof(float), cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(angle_ori, ang.p, px * sizeof(float), cudaMemcpyDeviceToHost, st));
     if (angle)
-        CK(cudaMemcpyAsync(angle, d_q, px, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(angle, q.p, px, cudaMemcpyDeviceToHost, st));
     if (src_level)
-        CK(cudaMemcpyAsync(src_level, d_a, px * ch, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(src_level, a.p, px * ch, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
-    cudaFree(d_a), cudaFree(d_q), cudaFree(d_mag), cudaFree(d_ang);
     if (w_out)
         *w_out = lw;
     if (h_out)

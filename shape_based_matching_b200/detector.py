@@ -179,6 +179,9 @@ class Detector:
         flight so that host->device copies overlap the kernels.  frames: sequence of HxW[xC] uint8 arrays (or one
         [N,H,W,C] array; pinned memory keeps the copies asynchronous).  Returns a list of MATCH_REC arrays, one
         per frame, each identical to match_records(frame)."""
+        return self._batch(self._L.sbm_match_batch, frames, threshold, class_ids, masks, cap, len(frames))
+
+    def _batch(self, fn, frames, threshold, class_ids, masks, cap, lists):
         imgs = [self._img(f) for f in frames]
         n = len(imgs)
         if n == 0:
@@ -200,17 +203,16 @@ class Detector:
                     keep.append(m)
             mptrs = (C.c_void_p * n)(*[(m.ctypes.data if m is not None else None) for m in keep])
         arr, ncls, _keep = self._class_args(class_ids)
-        cap = cap or 256 * n
-        begin = (C.c_int * (n + 1))()
+        cap = cap or 256 * lists
+        begin = (C.c_int * (lists + 1))()
         while True:
             out = np.zeros(cap, MATCH_REC)
-            rc = self._L.sbm_match_batch(self._h, ptrs, mptrs, n, w, h, c, 0, C.c_float(threshold), arr, ncls,
-                                         out.ctypes.data_as(C.c_void_p), cap, begin)
-            if rc == -3 and begin[n] > cap:
-                cap = begin[n]
+            rc = fn(self._h, ptrs, mptrs, n, w, h, c, 0, C.c_float(threshold), arr, ncls, out.ctypes.data_as(C.c_void_p), cap, begin)
+            if rc == -3 and begin[lists] > cap:
+                cap = begin[lists]
                 continue
             check(rc)
-            return [out[begin[i] : begin[i + 1]].copy() for i in range(n)]
+            return [out[begin[i] : begin[i + 1]].copy() for i in range(lists)]
 
     # ---- device-resident path (bench `value`, multi-GPU) ----------------------------------------
     def match_batch_device(self, d_imgs_ptr, frame_stride, n_frames, w, h, channels, threshold, class_ids, d_records, cap_per_frame,
@@ -286,6 +288,77 @@ class Detector:
         check(self._L.sbm_finalize_records(self._h, recs.ctypes.data_as(C.c_void_p), recs.shape[0], arr, n, int(finalize),
                                            out.ctypes.data_as(C.c_void_p), cap, C.byref(n_out)))
         return out[: n_out.value].copy()
+
+    def set_candidate_capacity(self, records):
+        """records each pipeline stage may hold per frame inside the context (sbm_set_candidate_capacity)"""
+        check(self._L.sbm_set_candidate_capacity(self._h, int(records)))
+
+    # ---- multi-GPU group: one Detector per GPU, NCCL behind the C ABI (sbm_group_*) ---------------
+    @staticmethod
+    def group_unique_id():
+        """128 bytes from rank 0 (ncclGetUniqueId) that every rank hands to group_create"""
+        buf = C.create_string_buffer(_capi.GROUP_ID_BYTES)
+        check(_capi.lib().sbm_group_unique_id(buf))
+        return buf.raw
+
+    def group_create(self, n_ranks, rank, unique_id, mode=_capi.GROUP_TEMPLATES):
+        """join a group of n_ranks detectors (collective).  Template modes: keep calling setClassTemplates with the
+        FULL classes on every rank, the context keeps this rank's slice."""
+        assert len(unique_id) == _capi.GROUP_ID_BYTES
+        check(self._L.sbm_clear_templates(self._h))
+        self._dirty = True
+        check(self._L.sbm_group_create(self._h, int(n_ranks), int(rank), C.c_char_p(unique_id), int(mode)))
+        self._group = (int(n_ranks), int(rank), int(mode))
+
+    def group_destroy(self):
+        check(self._L.sbm_group_destroy(self._h))
+        self._group = None
+        self._dirty = True
+
+    def group_info(self):
+        return getattr(self, "_group", None)
+
+    def group_match_records(self, source, threshold, class_ids=(), masks=None, cap=4096):
+        """Detector::match with the templates sharded over the group: the unsharded final list, on every rank"""
+        return self._run(self._L.sbm_group_match, source, threshold, class_ids, masks, cap)
+
+    def group_match_batch(self, frames, threshold, class_ids=(), masks=None, cap=None):
+        """sbm_group_match_batch: template sharding -> one list per frame; frame sharding -> the lists of all ranks'
+        frames, rank-major (every rank passes the same number of frames)"""
+        n_ranks, _rank, mode = self._group
+        lists = len(frames) * (n_ranks if mode == _capi.GROUP_FRAMES else 1)
+        return self._batch(self._L.sbm_group_match_batch, frames, threshold, class_ids, masks, cap, lists)
+
+    @staticmethod
+    def group_block_bytes(cap_per_frame):
+        return int(_capi.lib().sbm_group_block_bytes(int(cap_per_frame)))
+
+    def group_match_batch_device(self, d_imgs_ptr, frame_stride, n_frames, w, h, channels, threshold, class_ids, d_gathered, cap_per_frame,
+                                 stream=0):
+        """device-resident, asynchronous on `stream`: d_gathered = uint8 [n_ranks][n_frames][group_block_bytes(cap)]"""
+        arr, n, _keep = self._class_args(class_ids)
+        check(self._L.sbm_group_match_batch_device(self._h, C.c_void_p(d_imgs_ptr), frame_stride, n_frames, w, h, channels,
+                                                   C.c_float(threshold), arr, n, C.c_void_p(d_gathered), cap_per_frame,
+                                                   C.c_void_p(stream) if stream else None))
+
+    def group_finalize(self, h_gathered, n_frames, cap_per_frame, class_ids=(), finalize=True, cap=None):
+        """host copy of d_gathered -> list of MATCH_REC arrays (laid out like group_match_batch's result)"""
+        n_ranks, _rank, mode = self._group
+        lists = n_frames * (n_ranks if mode == _capi.GROUP_FRAMES else 1)
+        h = np.ascontiguousarray(h_gathered, dtype=np.uint8).ravel()
+        assert h.size == n_ranks * n_frames * self.group_block_bytes(cap_per_frame)
+        arr, n, _keep = self._class_args(class_ids)
+        cap = cap or max(256 * lists, 1)
+        begin = (C.c_int * (lists + 1))()
+        while True:
+            out = np.zeros(cap, MATCH_REC)
+            rc = self._L.sbm_group_finalize(self._h, h.ctypes.data_as(C.c_void_p), n_frames, cap_per_frame, arr, n, int(bool(finalize)),
+                                            out.ctypes.data_as(C.c_void_p), cap, begin)
+            if rc == -3 and begin[lists] > cap and "output holds" in _capi.lib().sbm_last_error().decode():
+                cap = begin[lists]
+                continue
+            check(rc)
+            return [out[begin[i] : begin[i + 1]].copy() for i in range(lists)]
 
     # ---- taps for parity tests ------------------------------------------------------------------
     def set_debug(self, on=True):

@@ -44,21 +44,25 @@ def shard_templates(tdesc, feats, rank, world, mode=INTERLEAVED):
     return np.ascontiguousarray(tdesc[ids]), np.ascontiguousarray(f)
 
 
-def merge_shard_records(recs_per_rank, class_sizes, mode=INTERLEAVED, finalize=True):
-    """recs_per_rank: list (rank order) of DEVICE_REC arrays; class_sizes[rank][class slot] = templates installed.
-    -> MATCH_REC array with GLOBAL template ids: the list the unsharded Detector::match returns."""
+def merge_shard_records(recs_per_rank, class_sizes, mode=INTERLEAVED, finalize=True, class_order=None):
+    """recs_per_rank: list (rank order) of DEVICE_REC arrays; class_sizes[rank][class slot] = templates installed, for
+    EVERY installed class slot in slot (= sorted id) order; class_order: the caller's class list as slot indices
+    (repeats allowed; None = every slot once).  -> MATCH_REC array with GLOBAL template ids: the list the unsharded
+    Detector::match returns."""
     L = _capi.lib()
     world = len(recs_per_rank)
     counts = np.array([len(r) for r in recs_per_rank], np.int32)
     allr = np.concatenate([np.ascontiguousarray(r, dtype=DEVICE_REC) for r in recs_per_rank]) if world else np.zeros(0, DEVICE_REC)
     allr = np.ascontiguousarray(allr)
     cs = np.ascontiguousarray(np.asarray(class_sizes, np.int32).reshape(world, -1))
-    cap = max(1, int(counts.sum()))
+    order = None if class_order is None else np.ascontiguousarray(class_order, np.int32)
+    cap = max(1, int(counts.sum()) * (1 if order is None else max(1, len(order))))
     out = np.zeros(cap, MATCH_REC)
     n_out = C.c_int()
     check(L.sbm_merge_shard_records(allr.ctypes.data_as(C.c_void_p), counts.ctypes.data_as(C.c_void_p), world,
-                                    cs.ctypes.data_as(C.c_void_p), cs.shape[1], int(mode), int(bool(finalize)),
-                                    out.ctypes.data_as(C.c_void_p), cap, C.byref(n_out)))
+                                    cs.ctypes.data_as(C.c_void_p), cs.shape[1], int(mode),
+                                    None if order is None else order.ctypes.data_as(C.c_void_p), 0 if order is None else len(order),
+                                    int(bool(finalize)), out.ctypes.data_as(C.c_void_p), cap, C.byref(n_out)))
     return out[: n_out.value].copy()
 
 
@@ -85,55 +89,47 @@ def allgather_records(recs, count, cap, group=None):
     return out, overflow
 
 
+def broadcast_unique_id(group=None):
+    """rank 0's NCCL unique id (sbm_group_unique_id) on every rank.  torch.distributed is only the messenger here: the
+    exchange of the match path itself runs inside the C ABI."""
+    import torch.distributed as dist
+
+    from .detector import Detector
+
+    box = [Detector.group_unique_id() if dist.get_rank(group) == 0 else None]
+    dist.broadcast_object_list(box, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+    return box[0]
+
+
 class ShardedDetector:
-    """Detector::match with the template set sharded over the ranks of a torch.distributed group.  Same template
-    store calls as Detector; match() returns the full (global) final list on every rank."""
+    """Detector::match with the template set sharded over the ranks of a group (one process per GPU).  Same template
+    store calls as Detector -- every rank is handed the FULL classes, the context keeps its slice -- and match()
+    returns the full final list on every rank.  The allgather and the merge run inside the C ABI (sbm_group_match);
+    torch.distributed only carries the 128-byte NCCL id at construction."""
 
     def __init__(self, num_features=63, T=(4, 8), weak_thresh=30.0, strong_thresh=60.0, device=0, group=None, mode=INTERLEAVED,
-                 rec_cap=8192):
-        import torch.distributed as dist
-
+                 unique_id=None, rank=None, world=None):
         from .detector import Detector
 
-        self.group = group
-        self.rank = dist.get_rank(group)
-        self.world = dist.get_world_size(group)
-        self.mode = mode
-        self.rec_cap = rec_cap
+        if unique_id is None:
+            import torch.distributed as dist
+
+            rank, world = dist.get_rank(group), dist.get_world_size(group)
+            unique_id = broadcast_unique_id(group)
+        self.rank, self.world, self.mode = int(rank), int(world), mode
         self.det = Detector(num_features, T, weak_thresh, strong_thresh, device=device)
+        self.det.group_create(self.world, self.rank, unique_id, mode)
         self.device = device
-        self._sizes = {}  # class id -> global template count
 
     def setClassTemplates(self, class_id, tdesc, feats):
-        tdesc = np.asarray(tdesc)
-        self._sizes[class_id] = tdesc.shape[0]
-        td, ft = shard_templates(tdesc, feats, self.rank, self.world, self.mode)
-        self.det.setClassTemplates(class_id, td, ft)
+        self.det.setClassTemplates(class_id, tdesc, feats)
 
-    def class_sizes(self, class_ids):
-        ids = list(class_ids) if class_ids else sorted(self._sizes)
-        return [[len(shard_ids(self._sizes[c], r, self.world, self.mode)) for c in ids] for r in range(self.world)]
+    def match(self, frame, threshold, class_ids=(), masks=None):
+        """frame: HxW[xC] uint8 numpy array, the same on every rank -> global final MATCH_REC list"""
+        return self.det.group_match_records(frame, threshold, class_ids, masks)
 
-    def match_device(self, d_img, w, h, channels, threshold, class_ids, d_recs, d_cnt, stream=0):
-        """enqueue this rank's shard on `stream`; results stay in the given device tensors"""
-        self.det.match_device(d_img, w, h, channels, threshold, class_ids, d_records=d_recs.data_ptr(), cap=self.rec_cap,
-                              d_count=d_cnt.data_ptr(), stream=stream)
+    def match_batch(self, frames, threshold, class_ids=()):
+        return self.det.group_match_batch(frames, threshold, class_ids)
 
-    def match(self, frame, threshold, class_ids=()):
-        """frame: HxWxC uint8 numpy array, the same on every rank -> global final MATCH_REC list"""
-        import torch
-
-        dev = torch.device("cuda", self.device)
-        img = np.ascontiguousarray(frame)
-        if img.ndim == 2:
-            img = img[:, :, None]
-        h, w, c = img.shape
-        d_img = torch.from_numpy(img).to(dev)
-        d_recs = torch.zeros(self.rec_cap * DEVICE_REC.itemsize, dtype=torch.uint8, device=dev)
-        d_cnt = torch.zeros(2, dtype=torch.int32, device=dev)
-        stream = torch.cuda.current_stream(dev).cuda_stream
-        self.match_device(d_img.data_ptr(), w, h, c, threshold, class_ids, d_recs, d_cnt, stream)
-        recs, overflow = allgather_records(d_recs, d_cnt, self.rec_cap, self.group)
-        if overflow:
-            raise _capi.SbmError(-3, "a shard produced more than rec_cap=%d records" % self.rec_cap)
-        return merge_shard_records(recs, self.class_sizes(class_ids), self.mode, True)
+    def close(self):
+        self.det.close()

@@ -212,3 +212,65 @@ def test_frames_smaller_than_a_kernel_tile(shape, T):
     hw = ((shape[0] >> lv) // T[lv], (shape[1] >> lv) // T[lv])
     for t in range(4):
         assert np.array_equal(det.similarity_map("s", t, hw), orc.similarity("s", t)), t
+
+
+def test_stage_overflow_on_the_device_path_raises_the_flag():
+    """more than 65536 coarse candidates in one frame (threshold -1: every position of every template passes).  The host
+    path grows its stage buffers and returns the complete list; the device-resident paths cannot synchronise, so they must
+    raise the overflow flag (d_count[1]) instead of handing back a silently truncated, atomically ordered subset -- on the
+    graph path, on the eager path (mask) and for batches -- until sbm_set_candidate_capacity makes room."""
+    import torch
+
+    from shape_based_matching_b200 import DEVICE_REC, Detector
+
+    rng = np.random.default_rng(8)
+    T = (4, 8)
+    img = synth_image(rng, 512, 512, 1)
+    tdesc, feats = synth_templates(rng, 80, 2, (40, 36), 12)
+    det = Detector(12, T, 30.0, 60.0)
+    det.setClassTemplates("a", tdesc, feats)
+    orc = Expected(T, 30.0, [("a", tdesc, feats)], num_features=12).process(img)
+    want = orc.match(-1.0, ["a"], finalize=False)
+    assert len(want) > 65536
+    h, w = img.shape[:2]
+    d_img = torch.from_numpy(img).cuda()
+    cap = 1 << 17
+    recs = torch.zeros(cap * DEVICE_REC.itemsize, dtype=torch.uint8, device="cuda")
+    cnt = torch.zeros(2, dtype=torch.int32, device="cuda")
+    full = np.full((h, w), 255, np.uint8)
+    d_mask = torch.from_numpy(full).cuda()
+    st = torch.cuda.Stream()
+
+    def device_run(mask_ptr=0):
+        cnt.zero_()
+        torch.cuda.synchronize()
+        det.match_device(d_img.data_ptr(), w, h, 1, -1.0, ["a"], d_records=recs.data_ptr(), cap=cap, d_count=cnt.data_ptr(),
+                         stream=st.cuda_stream, d_mask=mask_ptr)
+        st.synchronize()
+        return [int(v) for v in cnt.cpu()]
+
+    n, flag = device_run()
+    assert flag == 1, "graph path: %d records reported without the overflow flag" % n
+    n, flag = device_run(d_mask.data_ptr())
+    assert flag == 1, "eager path: %d records reported without the overflow flag" % n
+    # batches: every frame's flag
+    frames = torch.stack([d_img, d_img])
+    brecs = torch.zeros(2 * cap * DEVICE_REC.itemsize, dtype=torch.uint8, device="cuda")
+    bcnt = torch.zeros((2, 2), dtype=torch.int32, device="cuda")
+    det.match_batch_device(frames.data_ptr(), h * w, 2, w, h, 1, -1.0, ["a"], brecs.data_ptr(), cap, bcnt.data_ptr(), st.cuda_stream)
+    st.synchronize()
+    assert bcnt.cpu()[:, 1].tolist() == [1, 1]
+    # the host path grows and returns everything, in the reference's order
+    same_list(det.match_candidates(img, -1.0, ["a"], cap=1 << 17), want)
+    # room made: the device path now returns the complete multiset with the flag down
+    det.set_candidate_capacity(1 << 17)
+    for mask_ptr in (0, d_mask.data_ptr()):
+        n, flag = device_run(mask_ptr)
+        assert flag == 0 and n == len(want)
+        got = det.finalize_records(recs.cpu().numpy().view(DEVICE_REC)[:n], ["a"], finalize=False)
+        same_list(got, want)
+    # a caller buffer that is too small still raises it
+    cnt.zero_()
+    det.match_device(d_img.data_ptr(), w, h, 1, -1.0, ["a"], d_records=recs.data_ptr(), cap=1000, d_count=cnt.data_ptr(), stream=st.cuda_stream)
+    st.synchronize()
+    assert int(cnt.cpu()[1]) == 1 and int(cnt.cpu()[0]) == len(want)

@@ -139,3 +139,46 @@ def test_merge_rejects_bad_input():
     with pytest.raises(SbmError):
         merge_shard_records([bad, np.zeros(0, DEVICE_REC)], [[2], [2]])
     assert len(merge_shard_records([np.zeros(0, DEVICE_REC)] * 2, [[2], [2]])) == 0
+
+
+@pytest.mark.parametrize("world,mode", [(2, 0), (3, 1)])
+def test_two_class_merge_follows_the_request_order(world, mode):
+    """class_sizes covers EVERY installed class slot in slot order; the caller's class list (order, subsets) goes in
+    separately, like Detector::match appends class by class in request order (line2Dup.cpp:1124-1140).  Expected lists:
+    the reference's own two-class outputs (tests/golden/masked_two_class.npz)."""
+    from _fixtures import load_masked_two_class
+
+    from shape_based_matching_b200 import DEVICE_REC
+    from shape_based_matching_b200.sharding import merge_shard_records, shard_ids
+
+    z = load_masked_two_class()
+    slots = sorted(c[0] for c in z["classes"])  # a_ring, circle
+    n_of = {c[0]: c[1].shape[0] for c in z["classes"]}
+    sizes = [[len(shard_ids(n_of[s], r, world, mode)) for s in slots] for r in range(world)]
+    for tag, req in z["requests"]:
+        order = [slots.index(c) for c in req] if req else None
+        # the device lists hold each installed-and-matched class ONCE, whatever the request repeats
+        uniq = sorted(set(order)) if order is not None else list(range(len(slots)))
+        base = z["candidates_" + tag]
+        per_rank = []
+        for r in range(world):
+            rows = []
+            for k in uniq:
+                ids = shard_ids(n_of[slots[k]], r, world, mode)
+                local_of = {int(g): i for i, g in enumerate(ids)}
+                gid0 = sum(sizes[r][:k])
+                seen = set()
+                for j, c in enumerate(base):
+                    if int(c["class_idx"]) == k and int(c["template_id"]) in local_of:
+                        key = (int(c["x"]), int(c["y"]), int(c["template_id"]), j)
+                        rows.append((int(c["x"]), int(c["y"]), float(c["similarity"]), gid0 + local_of[int(c["template_id"])], j))
+                        seen.add(key)
+            recs = np.array(rows, dtype=DEVICE_REC) if rows else np.zeros(0, DEVICE_REC)
+            np.random.default_rng(r).shuffle(recs)
+            per_rank.append(recs)
+        for finalize, want in ((False, base), (True, z["matches_" + tag])):
+            got = merge_shard_records(per_rank, sizes, mode, finalize, class_order=order)
+            assert len(got) == len(want), (tag, finalize, len(got), len(want))
+            for f in ("x", "y", "template_id", "class_idx"):
+                assert np.array_equal(got[f], want[f]), (tag, finalize, f)
+            assert np.array_equal(got["similarity"].view(np.uint32), want["similarity"].view(np.uint32))
