@@ -271,6 +271,7 @@ def test_stage_overflow_on_the_device_path_raises_the_flag():
         same_list(got, want)
     # a caller buffer that is too small still raises it
     cnt.zero_()
+    torch.cuda.synchronize()
     det.match_device(d_img.data_ptr(), w, h, 1, -1.0, ["a"], d_records=recs.data_ptr(), cap=1000, d_count=cnt.data_ptr(), stream=st.cuda_stream)
     st.synchronize()
     assert int(cnt.cpu()[1]) == 1 and int(cnt.cpu()[0]) == len(want)
