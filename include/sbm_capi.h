@@ -233,8 +233,9 @@ int sbm_quantized_orientations(sbm_ctx *ctx, const uint8_t *img, int w, int h, i
 
 /* Counters of the most recent frame: [0] coarse evaluations (sum over matched templates of
  * in-image features * template_positions), [1] coarse candidates, [2] local evaluations,
- * [3] records after refinement, [4] kernels launched by the most recent call, [5] 1 when the coarsest level's
- * linear memories hold two responses per byte for the current frame shape (its W is even; k_similarity_nib),
+ * [3] records after refinement, [4] kernels launched by the most recent call, [5] layout of the coarsest level's linear
+ * memories for the current frame shape: 2 = hit / any bit planes (its W is a multiple of 32; k_similarity_bits), 1 = two
+ * responses per byte (W even; k_similarity_nib), 0 = one byte per response (k_similarity),
  * [6] 1 when level 0 is stored tiled for the refinement (its W is a multiple of 16; k_refine_tiled). */
 int sbm_last_stats(sbm_ctx *ctx, uint64_t stats[8]);
 

@@ -111,6 +111,7 @@ struct LevelGeom
     int T = 0, w = 0, h = 0, W = 0, H = 0;
     size_t lm_bytes = 0, lm_alloc = 0;
     bool nib = false; // memories packed two responses per byte (the coarsest level when W is even): k_similarity_nib reads them
+    bool bits = false; // memories as hit / any bit planes (the coarsest level when W % 32 == 0): k_similarity_bits reads them
     bool tiled = false; // memories tiled 8 rows x 16 bytes per 128-byte line (refined levels with W % 16 == 0): k_refine_tiled
 };
 
@@ -206,6 +207,13 @@ struct sbm_ctx
     uint32_t *d_coff = nullptr;
     std::vector<TemplCoarse> h_tcoarse;
 
+    // k_similarity_bits: one SimItem per active template for the current threshold (see ensureSimItems)
+    SimItem *d_sim_items = nullptr;
+    uint32_t sim_items_cap = 0;
+    uint64_t sim_epoch = 0;
+    float sim_threshold = 0.f;
+    int max_coarse_valid = 0; // most in-image coarse features any template has (selects the counter width)
+
     // active template list
     std::vector<int> active_classes; // as requested (may repeat)
     bool active_dirty = true;
@@ -281,6 +289,16 @@ bool coarseNibbles()
     return on;
 }
 
+// SBM_COARSE_BITS=0 keeps the byte / nibble layouts at the coarsest level whatever its width
+bool coarseBits()
+{
+    static const bool on = [] {
+        const char *e = getenv("SBM_COARSE_BITS");
+        return !(e && atoi(e) == 0);
+    }();
+    return on;
+}
+
 // SBM_REFINE_TILED=0 keeps the refined levels flat (k_refine) whatever their shape, =1 tiles them where the shape allows
 #ifndef SBM_REFINE_TILED_DEFAULT
 #define SBM_REFINE_TILED_DEFAULT 1
@@ -315,7 +333,15 @@ int ensureShape(sbm_ctx *c, int w, int h, int ch)
         // coarse scan past template_positions, 16 rows + 16 for the local patch, + the realigning vector loads
         // (K5a runs whole warps: up to 31 lanes x 16 positions beyond the last reported one)
         G.lm_alloc = G.lm_bytes + std::max(WH, (size_t)16 * G.W + 16) + 1024;
-        G.nib = l == c->levels - 1 && (G.W & 1) == 0 && coarseNibbles();
+        G.bits = l == c->levels - 1 && (G.W & 31) == 0 && coarseBits();
+        G.nib = !G.bits && l == c->levels - 1 && (G.W & 1) == 0 && coarseNibbles();
+        if (G.bits)
+        {
+            // 2 bits per position; behind the memories: the zero words the padded offsets read (two parity classes), a
+            // whole map for the scan past template_positions, and a tile + a warp of positions for the whole-warp loads
+            const size_t positions = (G.lm_bytes + 63) / 64 * 64 + 64 + (WH + K5B_TILE - 1) / K5B_TILE * K5B_TILE + 2 * K5B_TILE;
+            G.lm_alloc = positions / 4 + 256;
+        }
         // K5b's levels: tiles need whole 16-byte segments per row and an orientation stride of whole tile rows
         G.tiled = l < c->levels - 1 && (G.W & 15) == 0 && (((size_t)G.T * G.T * G.H) & 7) == 0 && refineTiled();
         if (G.tiled) // rows up to 16 (+1 for the wrap) behind the last memory, rounded up to a tile row
@@ -497,6 +523,7 @@ int ensureTemplates(sbm_ctx *c)
         const int T = G.T, W = G.W, H = G.H;
         const uint32_t WH = (uint32_t)W * H;
         c->h_tcoarse.assign(c->n_templates, TemplCoarse());
+        c->max_coarse_valid = 0;
         std::vector<uint32_t> off;
         uint32_t gid = 0;
         for (auto &cs : c->classes)
@@ -526,20 +553,24 @@ int ensureTemplates(sbm_ctx *c)
                             uint32_t a = (uint32_t)f.label * T * T * WH + (uint32_t)((f.y % T) * T + f.x % T) * WH +
                                          (uint32_t)(f.y / T) * W + (uint32_t)(f.x / T);
                             // k_similarity_nib has two shift classes (bit 3 of the offset): buckets 1 and 3 only, half the padding
-                            cls[G.nib ? ((a >> 3) & 1) * 2 + 1 : (a >> 2) & 3].push_back(a);
+                            // k_similarity_bits: the parity of the stream's first word pair (bit 5), buckets 1 and 3 as well
+                            cls[G.bits ? ((a >> 5) & 1) * 2 + 1 : G.nib ? ((a >> 3) & 1) * 2 + 1 : (a >> 2) & 3].push_back(a);
                         }
                         int nv = 0, stored = 0;
                         for (int k = 0; k < 4; ++k)
                         {
                             nv += (int)cls[k].size();
                             // pad with reads of the zeroed tail (same word shift): adds 0, keeps batches full
+                            // (bit planes: the zero words behind the memories, first pair even for bucket 1, odd for bucket 3)
+                            const uint32_t zero_off = G.bits ? (uint32_t)((G.lm_bytes + 63) / 64 * 64) + (k == 3 ? 32u : 0u) : (uint32_t)G.lm_bytes + 4u * k;
                             while (cls[k].size() % K5_U)
-                                cls[k].push_back((uint32_t)G.lm_bytes + 4u * k);
+                                cls[k].push_back(zero_off);
                             off.insert(off.end(), cls[k].begin(), cls[k].end());
                             stored += (int)cls[k].size();
                             o.cls_end[k] = (uint16_t)stored;
                         }
                         o.n_valid = nv;
+                        c->max_coarse_valid = std::max(c->max_coarse_valid, nv);
                     }
                     fo += d.num_features;
                 }
@@ -604,8 +635,6 @@ int ensureActive(sbm_ctx *c, const int *class_idx, int n_classes)
 
 // everything a match call needs before it can enqueue on slot s
 cudaError_t launchSpread(const LevelGeom &G, const uint8_t *quant, uint8_t *lm, uint8_t *dbg_spread, uint8_t *dbg_resp, cudaStream_t st);
-cudaError_t launchSimilarity(bool nib, dim3 grid, const uint8_t *lm, const uint32_t *coff, const TemplCoarse *tc, const uint32_t *active, int W,
-                             int HW, int T, float threshold, Cand *out, uint32_t *counter, uint32_t cap, uint16_t *dump, cudaStream_t st);
 cudaError_t launchRefine(bool tiled, int grid, const uint8_t *lm, const TemplLevel *tl, const Feat *feats, const Cand *in, const uint32_t *in_count,
                          uint32_t in_cap, Cand *out, uint32_t *out_count, uint32_t out_cap, int w, int h, int T, float threshold, uint16_t *dump,
                          int raw_center, unsigned long long *local_evals, cudaStream_t st);
@@ -628,13 +657,135 @@ bool shardOwns(int t, int n, int rank, int world, int mode)
     return t >= b && t < b + shardCount(n, rank, world, mode);
 }
 
-int prepare(sbm_ctx *c, Slot &s, int w, int h, int ch, const int *class_idx, int n_classes)
+// smallest raw sum whose score passes:  (raw*100.f)/(4*nf) > threshold  (line2Dup.cpp:1206-1208), in the same IEEE single
+// operations as the kernels' score_of (min_passing_raw in sbm_kernels.cuh computes the same number on the device)
+int minPassingRawHost(int nf, float threshold)
+{
+    auto score = [nf](int raw) {
+        volatile float a = (float)raw * 100.f;
+        volatile float b = a / (float)(4 * nf);
+        return (float)b;
+    };
+    const int top = 4 * nf + 1;
+    if (!(score(top) > threshold))
+        return 0x7fffffff;
+    int lo = 0, hi = top; // score is monotone in raw
+    while (lo < hi)
+    {
+        const int mid = (lo + hi) / 2;
+        if (score(mid) > threshold)
+            hi = mid;
+        else
+            lo = mid + 1;
+    }
+    return lo;
+}
+
+SimItem makeSimItem(const sbm_ctx *c, uint32_t gid, float threshold)
+{
+    const TemplCoarse &t = c->h_tcoarse[gid];
+    SimItem it = {};
+    it.off_begin = t.off_begin;
+    it.tgid = gid;
+    it.nf = t.nf;
+    it.tp = t.tp;
+    it.rawmin = minPassingRawHost(t.nf, threshold);
+    it.n_even = t.cls_end[1];
+    it.n_off = t.cls_end[3];
+    return it;
+}
+
+// the per-active-template records k_similarity_bits reads, for this threshold
+int ensureSimItems(sbm_ctx *c, float threshold)
+{
+    if (c->geom.empty() || !c->geom[c->levels - 1].bits)
+        return 0;
+    if (c->sim_epoch == c->epoch && memcmp(&c->sim_threshold, &threshold, sizeof(float)) == 0)
+        return 0;
+    std::vector<uint32_t> act;
+    {
+        std::vector<int> uniq = c->active_classes;
+        std::sort(uniq.begin(), uniq.end());
+        uniq.erase(std::unique(uniq.begin(), uniq.end()), uniq.end());
+        for (int k : uniq)
+            for (uint32_t g = c->gid_begin[k]; g < c->gid_begin[k + 1]; ++g)
+                act.push_back(g);
+    }
+    std::vector<SimItem> items(act.size());
+    for (size_t i = 0; i < act.size(); ++i)
+        items[i] = makeSimItem(c, act[i], threshold);
+    CK(cudaDeviceSynchronize()); // frames in flight may still read the previous records
+    if (c->sim_items_cap < items.size() || !c->d_sim_items)
+    {
+        freeDev(c->d_sim_items);
+        c->sim_items_cap = (uint32_t)std::max<size_t>(1, items.size());
+        CK(cudaMalloc(&c->d_sim_items, c->sim_items_cap * sizeof(SimItem)));
+        ++c->epoch; // the pointer is baked into the slots' graphs
+    }
+    if (!items.empty())
+        CK(cudaMemcpy(c->d_sim_items, items.data(), items.size() * sizeof(SimItem), cudaMemcpyHostToDevice));
+    c->sim_epoch = c->epoch;
+    c->sim_threshold = threshold;
+    return 0;
+}
+
+int prepare(sbm_ctx *c, Slot &s, int w, int h, int ch, const int *class_idx, int n_classes, float threshold)
 {
     int rc;
     if ((rc = ensureShape(c, w, h, ch)) || (rc = ensureTemplates(c)) || (rc = ensureActive(c, class_idx, n_classes)) ||
-        (rc = ensureSlot(c, s)))
+        (rc = ensureSimItems(c, threshold)) || (rc = ensureSlot(c, s)))
         return rc;
     return 0;
+}
+
+// The coarse similarity launch of a level in whichever layout it has: function, shape and an argument block that
+// stays valid until the launch / graph node is created.  items: NULL = the context's active list.
+struct CoarseLaunch
+{
+    void *func = nullptr;
+    dim3 grid, block;
+    const uint8_t *lm;
+    const uint32_t *coff, *active;
+    const TemplCoarse *tc;
+    const SimItem *items;
+    int W, HW, T;
+    float threshold;
+    Cand *out;
+    uint32_t *counter;
+    uint32_t cap;
+    uint16_t *dump;
+    void *argv[12];
+};
+
+void makeCoarse(CoarseLaunch &L, const sbm_ctx *c, const uint8_t *lm, const SimItem *items, const uint32_t *active, uint32_t n_active, float threshold,
+                Cand *out, uint32_t *counter, uint32_t cap, uint16_t *dump)
+{
+    const LevelGeom &CG = c->geom[c->levels - 1];
+    L.lm = lm, L.coff = c->d_coff, L.active = active, L.tc = c->d_tcoarse, L.items = items ? items : c->d_sim_items;
+    L.W = CG.W, L.HW = CG.W * CG.H, L.T = CG.T, L.threshold = threshold, L.out = out, L.counter = counter, L.cap = cap, L.dump = dump;
+    if (CG.bits)
+    {
+        // counter planes: 127 features fit 7 planes, 1023 fit 10, 8191 fit 13
+        L.func = c->max_coarse_valid <= 127 ? (void *)k_similarity_bits<3> : c->max_coarse_valid <= 1023 ? (void *)k_similarity_bits<6> : (void *)k_similarity_bits<9>;
+        L.grid = dim3(n_active, (L.HW + K5B_TILE - 1) / K5B_TILE), L.block = dim3(K5B_THREADS);
+        void *a[] = {&L.lm, &L.coff, &L.items, &L.W, &L.HW, &L.T, &L.out, &L.counter, &L.cap, &L.dump};
+        memcpy(L.argv, a, sizeof(a));
+    }
+    else
+    {
+        L.func = CG.nib ? (void *)k_similarity_nib : (void *)k_similarity;
+        L.grid = dim3(n_active, (L.HW + K5_TILE - 1) / K5_TILE), L.block = dim3(K5_THREADS);
+        void *a[] = {&L.lm, &L.coff, &L.tc, &L.active, &L.W, &L.HW, &L.T, &L.threshold, &L.out, &L.counter, &L.cap, &L.dump};
+        memcpy(L.argv, a, sizeof(a));
+    }
+}
+
+cudaError_t launchCoarse(const sbm_ctx *c, const uint8_t *lm, const SimItem *items, const uint32_t *active, uint32_t n_active, float threshold, Cand *out,
+                         uint32_t *counter, uint32_t cap, uint16_t *dump, cudaStream_t st)
+{
+    CoarseLaunch L;
+    makeCoarse(L, c, lm, items, active, n_active, threshold, out, counter, cap, dump);
+    return cudaLaunchKernel(L.func, L.grid, L.block, L.argv, 0, st);
 }
 
 // Enqueue the whole pipeline for one frame resident at d_img on stream st, using slot s's scratch.
@@ -682,9 +833,7 @@ int enqueueFrame(sbm_ctx *c, Slot &s, const uint8_t *d_img, const uint8_t *d_mas
     uint32_t *out_cnt = (L == 1 && user_count) ? user_count : s.d_counts + 0;
     if (c->n_active > 0)
     {
-        dim3 g(c->n_active, (HW + K5_TILE - 1) / K5_TILE);
-        CK(launchSimilarity(CG.nib, g, s.lv[L - 1].d_lm, c->d_coff, c->d_tcoarse, c->d_active, CG.W, HW, CG.T, threshold, out, out_cnt, out_cap,
-                            nullptr, st));
+        CK(launchCoarse(c, s.lv[L - 1].d_lm, nullptr, c->d_active, c->n_active, threshold, out, out_cnt, out_cap, nullptr, st));
         ++launches;
     }
     if (c->timing)
@@ -749,8 +898,11 @@ template <typename... A> int addKernel(cudaGraph_t g, cudaGraphNode_t *node, con
     return 0;
 }
 
-void *spreadFunc(int T, bool nib, bool tiled)
+void *spreadFunc(int T, bool nib, bool tiled, bool bits)
 {
+    if (bits)
+        return T == 4 ? (void *)k_spread_linearize<4, false, false, true> : T == 8 ? (void *)k_spread_linearize<8, false, false, true>
+               : T == 2 ? (void *)k_spread_linearize<2, false, false, true> : (void *)k_spread_linearize<16, false, false, true>;
     if (nib)
         return T == 4 ? (void *)k_spread_linearize<4, true> : T == 8 ? (void *)k_spread_linearize<8, true>
                : T == 2 ? (void *)k_spread_linearize<2, true> : (void *)k_spread_linearize<16, true>;
@@ -773,22 +925,12 @@ cudaError_t launchRefine(bool tiled, int grid, const uint8_t *lm, const TemplLev
     return cudaLaunchKernel(refineFunc(tiled), dim3(grid), dim3(K6_THREADS), argv, 0, st);
 }
 
-void *similarityFunc(bool nib) { return nib ? (void *)k_similarity_nib : (void *)k_similarity; }
-
 cudaError_t launchSpread(const LevelGeom &G, const uint8_t *quant, uint8_t *lm, uint8_t *dbg_spread, uint8_t *dbg_resp, cudaStream_t st)
 {
     dim3 g2((G.w + K2_PW - 1) / K2_PW, (G.h + K2_PH - 1) / K2_PH);
     int w = G.w, h = G.h;
     void *argv[] = {(void *)&quant, (void *)&w, (void *)&h, (void *)&lm, (void *)&dbg_spread, (void *)&dbg_resp};
-    return cudaLaunchKernel(spreadFunc(G.T, G.nib, G.tiled), g2, dim3(K2_THREADS), argv, 0, st);
-}
-
-cudaError_t launchSimilarity(bool nib, dim3 grid, const uint8_t *lm, const uint32_t *coff, const TemplCoarse *tc, const uint32_t *active, int W,
-                             int HW, int T, float threshold, Cand *out, uint32_t *counter, uint32_t cap, uint16_t *dump, cudaStream_t st)
-{
-    void *argv[] = {(void *)&lm,        (void *)&coff, (void *)&tc,      (void *)&active, (void *)&W,   (void *)&HW,
-                    (void *)&T,         (void *)&threshold, (void *)&out, (void *)&counter, (void *)&cap, (void *)&dump};
-    return cudaLaunchKernel(similarityFunc(nib), grid, dim3(K5_THREADS), argv, 0, st);
+    return cudaLaunchKernel(spreadFunc(G.T, G.nib, G.tiled, G.bits), g2, dim3(K2_THREADS), argv, 0, st);
 }
 
 int buildGraph(sbm_ctx *c, Slot &s, const uint8_t *src0, float threshold, bool with_fetch)
@@ -852,7 +994,7 @@ int buildGraph(sbm_ctx *c, Slot &s, const uint8_t *src0, float threshold, bool w
             s.n_orient0 = n_or, s.f_orient0 = orientFunc(c->c, th), s.g_orient0 = g1;
         dim3 g2((G.w + K2_PW - 1) / K2_PW, (G.h + K2_PH - 1) / K2_PH);
         const uint8_t *qin = LB.d_quant;
-        if ((rc = addKernel(g, &n_sp, {n_or}, spreadFunc(G.T, G.nib, G.tiled), g2, dim3(K2_THREADS), qin, G.w, G.h, LB.d_lm, null_dbg, null_dbg)))
+        if ((rc = addKernel(g, &n_sp, {n_or}, spreadFunc(G.T, G.nib, G.tiled, G.bits), g2, dim3(K2_THREADS), qin, G.w, G.h, LB.d_lm, null_dbg, null_dbg)))
             return rc;
         spread_node[l] = n_sp;
         launches += 2;
@@ -866,15 +1008,15 @@ int buildGraph(sbm_ctx *c, Slot &s, const uint8_t *src0, float threshold, bool w
     uint32_t *in_cnt = s.d_counts + 0;
     if (c->n_active > 0)
     {
-        dim3 gs(c->n_active, (HW + K5_TILE - 1) / K5_TILE);
-        const uint8_t *lm = s.lv[L - 1].d_lm;
-        const uint32_t *coff = c->d_coff, *act = c->d_active;
-        const TemplCoarse *tc = c->d_tcoarse;
-        uint16_t *nodump = nullptr;
+        CoarseLaunch CL;
+        makeCoarse(CL, c, s.lv[L - 1].d_lm, nullptr, c->d_active, c->n_active, threshold, in, in_cnt, in_cap, nullptr);
         cudaGraphNode_t n_sim;
-        if ((rc = addKernel(g, &n_sim, {n_memset, spread_node[L - 1]}, similarityFunc(CG.nib), gs, dim3(K5_THREADS), lm, coff, tc, act, CG.W, HW, CG.T,
-                            threshold, in, in_cnt, in_cap, nodump)))
-            return rc;
+        {
+            const cudaGraphNode_t deps[2] = {n_memset, spread_node[L - 1]};
+            cudaKernelNodeParams kp = {};
+            kp.func = CL.func, kp.gridDim = CL.grid, kp.blockDim = CL.block, kp.sharedMemBytes = 0, kp.kernelParams = CL.argv, kp.extra = nullptr;
+            CK(cudaGraphAddKernelNode(&n_sim, g, deps, 2, &kp));
+        }
         tail = n_sim;
         ++launches;
     }
@@ -1142,7 +1284,7 @@ int matchHost(sbm_ctx *c, const uint8_t *img, int w, int h, int ch, size_t strid
     CK(cudaSetDevice(c->device));
     Slot &s = c->slot[0];
     int rc;
-    if ((rc = prepare(c, s, w, h, ch, class_idx, n_classes)))
+    if ((rc = prepare(c, s, w, h, ch, class_idx, n_classes, threshold)))
         return rc;
     const uint8_t *dm = nullptr;
     if ((rc = uploadFrame(s, img, w, h, ch, stride, mask, &dm)))
@@ -1360,7 +1502,7 @@ int groupEnqueue(sbm_ctx *c, const uint8_t *const *imgs, const uint8_t *const *m
     const int NS = frameSlots();
     const int ns = std::min(n_frames, NS);
     for (int k = 0; k < ns; ++k)
-        if ((rc = prepare(c, c->slot[k], w, h, ch, class_idx, n_classes)))
+        if ((rc = prepare(c, c->slot[k], w, h, ch, class_idx, n_classes, threshold)))
             return rc;
     const size_t blk = groupBlockBytes(cap);
     if ((rc = ensureGroupBuffers(c, blk * n_frames, d_gathered == nullptr)))
@@ -1559,7 +1701,7 @@ const char *sbm_build_info(void)
 #define SBM_STR2(x) #x
 #define SBM_STR(x) SBM_STR2(x)
     return "shape_based_matching_b200 csrc: nvcc " SBM_STR(__CUDACC_VER_MAJOR__) "." SBM_STR(__CUDACC_VER_MINOR__)
-           " -gencode arch=compute_100a,code=sm_100a; kernels k_orient k_pyrdown k_spread_linearize k_similarity_nib k_similarity k_refine_tiled k_refine";
+           " -gencode arch=compute_100a,code=sm_100a; kernels k_orient k_pyrdown k_spread_linearize k_similarity_bits k_similarity_nib k_similarity k_refine_tiled k_refine";
 }
 
 int sbm_create(const int *T, int levels, float weak, float strong, int num_features, int device, sbm_ctx **out)
@@ -1607,6 +1749,7 @@ int sbm_destroy(sbm_ctx *c)
     freeDev(c->d_tcoarse);
     freeDev(c->d_coff);
     freeDev(c->d_active);
+    freeDev(c->d_sim_items);
     delete c;
     return 0;
 }
@@ -1738,7 +1881,7 @@ int sbm_match_batch(sbm_ctx *c, const uint8_t *const *imgs, const uint8_t *const
         return 0;
     const int NS = frameSlots();
     for (int k = 0; k < std::min(n_frames, NS); ++k)
-        if ((rc = prepare(c, c->slot[k], w, h, ch, class_idx, n_classes)))
+        if ((rc = prepare(c, c->slot[k], w, h, ch, class_idx, n_classes, threshold)))
             return rc;
     const uint8_t *dm[SBM_SLOTS] = {nullptr};
     int used = 0;
@@ -1776,7 +1919,7 @@ int sbm_match_device(sbm_ctx *c, const void *d_img, int w, int h, int ch, const 
     CK(cudaSetDevice(c->device));
     Slot &s = c->slot[0];
     int rc;
-    if ((rc = prepare(c, s, w, h, ch, class_idx, n_classes)))
+    if ((rc = prepare(c, s, w, h, ch, class_idx, n_classes, threshold)))
         return rc;
     cudaStream_t st = stream ? (cudaStream_t)stream : s.stream;
     s.last_src0 = (const uint8_t *)d_img;
@@ -1799,7 +1942,7 @@ int sbm_match_batch_device(sbm_ctx *c, const void *d_imgs, size_t frame_stride, 
     const int NS = frameSlots();
     const int ns = std::min(n_frames, NS);
     for (int k = 0; k < ns; ++k)
-        if ((rc = prepare(c, c->slot[k], w, h, ch, class_idx, n_classes)))
+        if ((rc = prepare(c, c->slot[k], w, h, ch, class_idx, n_classes, threshold)))
             return rc;
     cudaStream_t user = (cudaStream_t)stream;
     // fork: every slot stream starts after the work already queued on the caller's stream
@@ -2078,6 +2221,15 @@ int sbm_get_intermediate(sbm_ctx *c, int level, int kind, void *dst, size_t byte
         cudaFree(d_bytes);
         return 0;
     }
+    if (kind == SBM_LINEAR && G.bits)
+    {
+        uint8_t *d_bytes = nullptr;
+        CK(cudaMalloc(&d_bytes, need));
+        k_unpack_bits<<<148 * 4, 256>>>(reinterpret_cast<const uint32_t *>(L.d_lm), d_bytes, need);
+        CK(cudaMemcpy(dst, d_bytes, need, cudaMemcpyDeviceToHost));
+        cudaFree(d_bytes);
+        return 0;
+    }
     if (kind == SBM_LINEAR && G.nib)
     {
         // the caller sees one byte per response whatever the device layout
@@ -2117,12 +2269,17 @@ int sbm_similarity_map(sbm_ctx *c, int class_idx, int template_id, uint16_t *dst
     CK(cudaMalloc(&d_dump, (size_t)HW * 2));
     CK(cudaMemcpy(d_one, &gid, 4, cudaMemcpyHostToDevice));
     CK(cudaMemset(d_cnt, 0, 4));
-    dim3 g(1, (HW + K5_TILE - 1) / K5_TILE);
-    CK(launchSimilarity(CG.nib, g, s.lv[c->levels - 1].d_lm, c->d_coff, c->d_tcoarse, d_one, CG.W, HW, CG.T, 1e30f, d_sink, d_cnt, 0, d_dump,
-                        s.stream));
+    SimItem *d_item = nullptr;
+    if (CG.bits) // the bit-plane kernel takes one record per template instead of (active[], tinfo[])
+    {
+        const SimItem it = makeSimItem(c, gid, 1e30f);
+        CK(cudaMalloc(&d_item, sizeof(SimItem)));
+        CK(cudaMemcpy(d_item, &it, sizeof(SimItem), cudaMemcpyHostToDevice));
+    }
+    CK(launchCoarse(c, s.lv[c->levels - 1].d_lm, d_item, d_one, 1, 1e30f, d_sink, d_cnt, 0, d_dump, s.stream));
     CK(cudaStreamSynchronize(s.stream));
     CK(cudaMemcpy(dst, d_dump, (size_t)HW * 2, cudaMemcpyDeviceToHost));
-    cudaFree(d_one), cudaFree(d_cnt), cudaFree(d_sink), cudaFree(d_dump);
+    cudaFree(d_one), cudaFree(d_cnt), cudaFree(d_sink), cudaFree(d_dump), cudaFree(d_item);
     return 0;
 }
 
@@ -2155,11 +2312,15 @@ int sbm_similarity_local(sbm_ctx *c, int class_idx, int template_id, int level, 
     CK(cudaMemset(d_ev, 0, 8));
     const uint8_t *lm = s.lv[level].d_lm;
     uint8_t *d_bytes = nullptr;
-    if (G.nib) // the coarsest level is never refined by the pipeline; the tap unpacks it first
+    if (G.nib || G.bits) // the coarsest level is never refined by the pipeline; the tap unpacks it first
     {
-        CK(cudaMalloc(&d_bytes, G.lm_alloc));
-        CK(cudaMemsetAsync(d_bytes, 0, G.lm_alloc, s.stream));
-        k_unpack_nibbles<<<148 * 4, 256, 0, s.stream>>>(lm, d_bytes, G.lm_bytes);
+        const size_t bytes = G.lm_bytes + std::max((size_t)G.W * G.H, (size_t)16 * G.W + 16) + 1024;
+        CK(cudaMalloc(&d_bytes, bytes));
+        CK(cudaMemsetAsync(d_bytes, 0, bytes, s.stream));
+        if (G.bits)
+            k_unpack_bits<<<148 * 4, 256, 0, s.stream>>>(reinterpret_cast<const uint32_t *>(lm), d_bytes, G.lm_bytes);
+        else
+            k_unpack_nibbles<<<148 * 4, 256, 0, s.stream>>>(lm, d_bytes, G.lm_bytes);
         lm = d_bytes;
     }
     CK(launchRefine(G.tiled, 1, lm, c->tl[level].d_tl, c->tl[level].d_feats, d_in, d_cnt, 1, d_out, d_cnt + 1, 1, G.w, G.h, G.T, 1e30f, d_dump, 1,
@@ -2178,7 +2339,7 @@ int sbm_last_stats(sbm_ctx *c, uint64_t stats[8])
     memcpy(stats, c->stats, sizeof(c->stats));
     stats[0] = c->coarse_evals;
     stats[4] = (uint64_t)c->slot[0].launches;
-    stats[5] = c->levels > 0 && c->geom[c->levels - 1].nib ? 1 : 0;
+    stats[5] = c->levels == 0 ? 0 : c->geom[c->levels - 1].bits ? 2 : c->geom[c->levels - 1].nib ? 1 : 0; // coarse layout
     stats[6] = c->levels > 1 && c->geom[0].tiled ? 1 : 0;
     return 0;
 }
@@ -2211,9 +2372,11 @@ int sbm_time_similarity(sbm_ctx *c, float threshold, int iters, float *ms_per_la
         return fail(SBM_ERR_STATE, "no frame has been processed");
     CK(cudaSetDevice(c->device));
     const int L = c->levels;
-    const LevelGeom &CG = c->geom[L - 1];
-    const int HW = CG.W * CG.H;
-    dim3 g(c->n_active, (HW + K5_TILE - 1) / K5_TILE);
+    {
+        int rc_i;
+        if ((rc_i = ensureSimItems(c, threshold)))
+            return rc_i;
+    }
     CK(cudaStreamSynchronize(s.stream));
     // `iters` launches as one captured graph (stream launches are CPU-paced on this host, tools/launch_quant.cu)
     cudaGraph_t tg = nullptr;
@@ -2221,8 +2384,7 @@ int sbm_time_similarity(sbm_ctx *c, float threshold, int iters, float *ms_per_la
     CK(cudaStreamBeginCapture(s.stream, cudaStreamCaptureModeThreadLocal));
     for (int i = 0; i < iters; ++i)
         // same launch as the pipeline's; the candidate counter keeps running, records beyond cap are dropped
-        CK(launchSimilarity(CG.nib, g, s.lv[L - 1].d_lm, c->d_coff, c->d_tcoarse, c->d_active, CG.W, HW, CG.T, threshold, s.d_buf[1],
-                            s.d_counts + 12, 0u, nullptr, s.stream));
+        CK(launchCoarse(c, s.lv[L - 1].d_lm, nullptr, c->d_active, c->n_active, threshold, s.d_buf[1], s.d_counts + 12, 0u, nullptr, s.stream));
     CK(cudaStreamEndCapture(s.stream, &tg));
     CK(cudaGraphInstantiate(&te, tg, 0));
     CK(cudaGraphLaunch(te, s.stream));
@@ -2286,6 +2448,11 @@ int sbm_time_kernels(sbm_ctx *c, float threshold, int iters, float *ms, int n_ms
     if (n_ms < 4 * L + 1)
         return fail(SBM_ERR_BAD_ARG, "ms[] needs %d entries", 4 * L + 1);
     CK(cudaSetDevice(c->device));
+    {
+        int rc_i;
+        if ((rc_i = ensureSimItems(c, threshold)))
+            return rc_i;
+    }
     cudaStream_t st = s.stream;
     CK(cudaStreamSynchronize(st));
     const float weak_sq = c->weak * c->weak;
@@ -2337,15 +2504,11 @@ int sbm_time_kernels(sbm_ctx *c, float threshold, int iters, float *ms, int n_ms
         uint8_t *nd = nullptr;
         SBM_TIME(3 * l + 2, (void)launchSpread(G, LB.d_quant, LB.d_lm, nd, nd, st));
     }
-    const LevelGeom &CG = c->geom[L - 1];
-    const int HW = CG.W * CG.H;
-    dim3 gs(c->n_active, (HW + K5_TILE - 1) / K5_TILE);
     // scratch counters so that the frame's real candidate counts stay intact
     uint32_t *d_tmp = nullptr;
     CK(cudaMalloc(&d_tmp, COUNT_WORDS * 4));
     CK(cudaMemsetAsync(d_tmp, 0, COUNT_WORDS * 4, st));
-    SBM_TIME(3 * L, (void)launchSimilarity(CG.nib, gs, s.lv[L - 1].d_lm, c->d_coff, c->d_tcoarse, c->d_active, CG.W, HW, CG.T, threshold, s.d_buf[1],
-                                           d_tmp, 0u, nullptr, st));
+    SBM_TIME(3 * L, (void)launchCoarse(c, s.lv[L - 1].d_lm, nullptr, c->d_active, c->n_active, threshold, s.d_buf[1], d_tmp, 0u, nullptr, st));
     // refinement of the frame's own coarse candidates (stage counts of the last real run), output discarded
     int stage = 1;
     for (int l = L - 2; l >= 0; --l, ++stage)

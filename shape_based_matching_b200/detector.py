@@ -392,7 +392,8 @@ class Detector:
         s = np.zeros(8, np.uint64)
         check(self._L.sbm_last_stats(self._h, s.ctypes.data_as(C.c_void_p)))
         return dict(coarse_evals=int(s[0]), coarse_candidates=int(s[1]), local_evals=int(s[2]), records=int(s[3]),
-                    gpu_launches=int(s[4]), coarse_nibbles=int(s[5]), refine_tiled=int(s[6]))
+                    gpu_launches=int(s[4]), coarse_nibbles=int(int(s[5]) == 1), coarse_layout=("byte", "nib", "bits")[int(s[5])],
+                    refine_tiled=int(s[6]))
 
     def last_timing(self):
         t = np.zeros(4, np.float32)

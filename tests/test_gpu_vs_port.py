@@ -1,6 +1,6 @@
 """GPU parity on seeded synthetic inputs: shapes, channel counts, T sets, pyramid depths and masks the fixtures do
 not cover.  Expectations come from tests/_refcheck.py: the reference's OWN code (oracle/_ref) for every configuration
-the reference accepts (15 of the 17 below), with the C++ restatement (oracle/sbm_oracle.cpp) run beside it and
+the reference accepts (all but two of those below), with the C++ restatement (oracle/sbm_oracle.cpp) run beside it and
 required to agree; the restatement alone only for the shapes the reference asserts on (odd coarse widths).
 Bar: byte-exact intermediates, identical candidate and final lists."""
 import numpy as np
@@ -61,6 +61,14 @@ CONFIGS = [
     (88, 104, 3, (4, 4), 6, (30, 26), 40, 25.0, False),      # level-0 W = 26 (W % 4 = 2): k_refine's per-row shift path
     (128, 192, 3, (4, 8), 6, (40, 36), 40, 30.0, True),      # level-0 W = 48: tiled level 0 (k_refine_tiled) with a mask
     (192, 256, 3, (8, 8), 5, (60, 50), 70, 10.0, False),     # T = 8 on both levels, level-0 W = 32: tiled writer for T = 8
+    # the coarsest level is stored as hit / any bit planes when its W is a multiple of 32 (k_similarity_bits):
+    (256, 512, 3, (4, 8), 8, (64, 48), 40, 30.0, False),     # T = 8 on top, W = 32 (16-cell ballots), < 128 features: 7-plane counters
+    (64, 128, 1, (4,), 6, (30, 30), 70, 30.0, True),         # T = 4 on top, W = 32 (whole-word ballots), masked
+    (48, 128, 3, (2,), 4, (20, 16), 16, 30.0, False),        # T = 2 on top, W = 64 (two words per cell row)
+    (64, 512, 1, (16,), 4, (60, 30), 20, 25.0, False),       # T = 16 on top, W = 32 (8-cell ballots)
+    (256, 512, 3, (4, 8), 4, (90, 70), 600, 20.0, False),    # 300 coarse features: 10-plane counters, odd / even parity classes
+    (512, 512, 1, (4, 8), 3, (200, 200), 4000, 10.0, False), # 2000 coarse features: 13-plane counters, two offset chunks
+    (128, 256, 3, (4,), 5, (40, 36), 24, 30.0, False),       # W = 64 = exactly one warp of 64-position threads per row pair
 ]
 
 
@@ -117,17 +125,20 @@ def test_local_patch_sums():
 
 
 def test_flat_byte_wide_layouts_by_environment():
-    """SBM_COARSE_NIBBLES=0 keeps k_similarity (one byte per response) on the coarsest level and SBM_REFINE_TILED=0
-    keeps k_refine (flat memories) on the refined levels for every shape: the same parity tests in a fresh process,
+    """SBM_COARSE_BITS=0 keeps k_similarity_nib (two responses per byte) where the default is bit planes;
+    SBM_COARSE_NIBBLES=0 on top keeps k_similarity (one byte per response) on the coarsest level and SBM_REFINE_TILED=0
+    keeps k_refine (flat memories) on the refined levels for every shape: the same parity tests in fresh processes,
     including the > 1024-offset chunks of the 8191-feature template"""
     import os
     import subprocess
     import sys
 
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    env = dict(os.environ, SBM_COARSE_NIBBLES="0", SBM_REFINE_TILED="0")
-    r = subprocess.run([sys.executable, "-m", "pytest", "-q", "-x", "-m", "gpu", "tests/test_gpu_vs_port.py::test_cuda_equals_port",
-                        "tests/test_gpu_edge_cases.py::test_feature_count_limit_8191",
-                        "tests/test_gpu_edge_cases.py::test_templates_larger_than_the_frame_and_features_outside", "tests/test_gpu_parity.py"],
-                       cwd=root, env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
-    assert r.returncode == 0, r.stdout[-3000:]
+    # 1: no bit planes -> the nibble-packed layout wherever W is even (M1, configurations 17-23); 2: bytes and flat everywhere
+    for extra in (dict(SBM_COARSE_BITS="0"), dict(SBM_COARSE_BITS="0", SBM_COARSE_NIBBLES="0", SBM_REFINE_TILED="0")):
+        env = dict(os.environ, **extra)
+        r = subprocess.run([sys.executable, "-m", "pytest", "-q", "-x", "-m", "gpu", "tests/test_gpu_vs_port.py::test_cuda_equals_port",
+                            "tests/test_gpu_edge_cases.py::test_feature_count_limit_8191",
+                            "tests/test_gpu_edge_cases.py::test_templates_larger_than_the_frame_and_features_outside", "tests/test_gpu_parity.py"],
+                           cwd=root, env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
+        assert r.returncode == 0, (extra, r.stdout[-3000:])
