@@ -126,7 +126,8 @@ struct LevelBuf
 {
     uint8_t *d_src = nullptr; // level >= 1 (level 0 is the frame itself)
     uint8_t *d_quant = nullptr;
-    uint8_t *d_lm = nullptr;
+    uint8_t *d_lm = nullptr;       // the level's linear memories (bit planes: K5B_FRONT bytes into the allocation)
+    uint8_t *d_lm_alloc = nullptr; // what cudaMalloc returned
     uint8_t *d_spread = nullptr, *d_resp = nullptr; // debug taps
 };
 
@@ -174,6 +175,9 @@ struct Slot
     void *f_orient0 = nullptr, *f_pyr1 = nullptr;
     dim3 g_orient0, g_pyr1;
     int graph_launches = 0;
+    Cand *graph_final = nullptr; // where the graph's last stage writes
+    uint32_t *graph_final_count = nullptr;
+    uint32_t graph_final_cap = 0;
 };
 } // namespace
 
@@ -182,6 +186,7 @@ struct sbm_ctx
     int device = 0;
     int sms = 148;                 // multiprocessors of `device`
     int refine_grid[2] = {0, 0};   // K5b grid (flat / tiled kernel) = CTAs resident at once on `device`
+    int bits_split_ctas[3][5] = {}; // k_similarity_bits<NH, SPLIT>: CTAs of 64 * K threads resident per SM, [NH variant][K]
     std::vector<int> T;
     float weak = 30.f, strong = 60.f;
     int num_features = 63;
@@ -210,6 +215,11 @@ struct sbm_ctx
     // k_similarity_bits: one SimItem per active template for the current threshold (see ensureSimItems)
     SimItem *d_sim_items = nullptr;
     uint32_t sim_items_cap = 0;
+    uint2 *d_sim_offs = nullptr; // [n_active][sim_stride] pre-decoded feature offsets of the active templates
+    size_t sim_offs_cap = 0;
+    uint32_t sim_stride = 8;
+    uint64_t sim_offs_epoch = 0;
+    std::vector<uint32_t> h_coff; // host copy of d_coff
     uint64_t sim_epoch = 0;
     float sim_threshold = 0.f;
     int max_coarse_valid = 0; // most in-image coarse features any template has (selects the counter width)
@@ -248,7 +258,8 @@ void freeSlotShape(Slot &s)
     {
         freeDev(l.d_src);
         freeDev(l.d_quant);
-        freeDev(l.d_lm);
+        freeDev(l.d_lm_alloc);
+        l.d_lm = nullptr;
         freeDev(l.d_spread);
         freeDev(l.d_resp);
     }
@@ -340,7 +351,7 @@ int ensureShape(sbm_ctx *c, int w, int h, int ch)
             // 2 bits per position; behind the memories: the zero words the padded offsets read (two parity classes), a
             // whole map for the scan past template_positions, and a tile + a warp of positions for the whole-warp loads
             const size_t positions = (G.lm_bytes + 63) / 64 * 64 + 64 + (WH + K5B_TILE - 1) / K5B_TILE * K5B_TILE + 2 * K5B_TILE;
-            G.lm_alloc = positions / 4 + 256;
+            G.lm_alloc = K5B_FRONT + positions / 4 + 256;
         }
         // K5b's levels: tiles need whole 16-byte segments per row and an orientation stride of whole tile rows
         G.tiled = l < c->levels - 1 && (G.W & 15) == 0 && (((size_t)G.T * G.T * G.H) & 7) == 0 && refineTiled();
@@ -398,8 +409,9 @@ int ensureSlot(sbm_ctx *c, Slot &s)
             if (l > 0)
                 CK(cudaMalloc(&L.d_src, px * c->c));
             CK(cudaMalloc(&L.d_quant, px));
-            CK(cudaMalloc(&L.d_lm, G.lm_alloc));
-            CK(cudaMemset(L.d_lm, 0, G.lm_alloc));
+            CK(cudaMalloc(&L.d_lm_alloc, G.lm_alloc));
+            CK(cudaMemset(L.d_lm_alloc, 0, G.lm_alloc));
+            L.d_lm = L.d_lm_alloc + (G.bits ? K5B_FRONT : 0);
             if (c->debug)
             {
                 CK(cudaMalloc(&L.d_spread, px));
@@ -554,7 +566,9 @@ int ensureTemplates(sbm_ctx *c)
                                          (uint32_t)(f.y / T) * W + (uint32_t)(f.x / T);
                             // k_similarity_nib has two shift classes (bit 3 of the offset): buckets 1 and 3 only, half the padding
                             // k_similarity_bits: the parity of the stream's first word pair (bit 5), buckets 1 and 3 as well
-                            cls[G.bits ? ((a >> 5) & 1) * 2 + 1 : G.nib ? ((a >> 3) & 1) * 2 + 1 : (a >> 2) & 3].push_back(a);
+                            // (a stream that starts on a word boundary is staged one pair earlier, see decodeOffsets)
+                            const uint32_t pair0 = (a >> 5) - ((a & 31u) == 0 ? 1u : 0u);
+                            cls[G.bits ? (pair0 & 1) * 2 + 1 : G.nib ? ((a >> 3) & 1) * 2 + 1 : (a >> 2) & 3].push_back(a);
                         }
                         int nv = 0, stored = 0;
                         for (int k = 0; k < 4; ++k)
@@ -562,7 +576,8 @@ int ensureTemplates(sbm_ctx *c)
                             nv += (int)cls[k].size();
                             // pad with reads of the zeroed tail (same word shift): adds 0, keeps batches full
                             // (bit planes: the zero words behind the memories, first pair even for bucket 1, odd for bucket 3)
-                            const uint32_t zero_off = G.bits ? (uint32_t)((G.lm_bytes + 63) / 64 * 64) + (k == 3 ? 32u : 0u) : (uint32_t)G.lm_bytes + 4u * k;
+                            // (bit planes: the zero words behind the memories, first pair even for bucket 1, odd for bucket 3)
+                            const uint32_t zero_off = G.bits ? (uint32_t)((G.lm_bytes + 63) / 64 * 64) + (k == 3 ? 33u : 1u) : (uint32_t)G.lm_bytes + 4u * k;
                             while (cls[k].size() % K5_U)
                                 cls[k].push_back(zero_off);
                             off.insert(off.end(), cls[k].begin(), cls[k].end());
@@ -584,6 +599,10 @@ int ensureTemplates(sbm_ctx *c)
             CK(cudaMemcpy(c->d_tcoarse, c->h_tcoarse.data(), c->h_tcoarse.size() * sizeof(TemplCoarse), cudaMemcpyHostToDevice));
         if (!off.empty())
             CK(cudaMemcpy(c->d_coff, off.data(), off.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+        if (G.bits)
+            c->h_coff.swap(off);
+        else
+            std::vector<uint32_t>().swap(c->h_coff);
         c->coarse_dirty = false;
         ++c->epoch;
         c->active_dirty = true;
@@ -685,7 +704,6 @@ SimItem makeSimItem(const sbm_ctx *c, uint32_t gid, float threshold)
 {
     const TemplCoarse &t = c->h_tcoarse[gid];
     SimItem it = {};
-    it.off_begin = t.off_begin;
     it.tgid = gid;
     it.nf = t.nf;
     it.tp = t.tp;
@@ -695,12 +713,31 @@ SimItem makeSimItem(const sbm_ctx *c, uint32_t gid, float threshold)
     return it;
 }
 
-// the per-active-template records k_similarity_bits reads, for this threshold
+// offsets of template gid as k_similarity_bits stages them: .x = byte offset of the first word pair, .y = bit shift
+void decodeOffsets(const sbm_ctx *c, uint32_t gid, uint2 *dst)
+{
+    const TemplCoarse &t = c->h_tcoarse[gid];
+    for (int i = 0; i < (int)t.cls_end[3]; ++i)
+    {
+        // stream of position j = bit (o + j) of the flat bit sequence: first pair k = o >> 5, shift s = o & 31; a shift of
+        // 0 is staged as (k - 1, 32) so that the multiplier 2^(32 - s) fits 32 bits (k5b_funnel)
+        const uint32_t o = c->h_coff[t.off_begin + i];
+        int64_t k = o >> 5;
+        uint32_t sft = o & 31u;
+        if (sft == 0)
+            --k, sft = 32;
+        dst[i] = make_uint2((uint32_t)((int64_t)K5B_FRONT + k * 8), 1u << (32 - sft));
+    }
+}
+
+// what k_similarity_bits reads per active template: the offsets (fixed stride; depend on the active list and the frame
+// shape) and the SimItem records (depend on the threshold as well)
 int ensureSimItems(sbm_ctx *c, float threshold)
 {
     if (c->geom.empty() || !c->geom[c->levels - 1].bits)
         return 0;
-    if (c->sim_epoch == c->epoch && memcmp(&c->sim_threshold, &threshold, sizeof(float)) == 0)
+    const bool offs_stale = c->sim_offs_epoch != c->epoch;
+    if (!offs_stale && c->sim_epoch == c->epoch && memcmp(&c->sim_threshold, &threshold, sizeof(float)) == 0)
         return 0;
     std::vector<uint32_t> act;
     {
@@ -711,20 +748,44 @@ int ensureSimItems(sbm_ctx *c, float threshold)
             for (uint32_t g = c->gid_begin[k]; g < c->gid_begin[k + 1]; ++g)
                 act.push_back(g);
     }
+    CK(cudaDeviceSynchronize()); // frames in flight may still read the previous arrays
+    bool realloc = false;
+    if (offs_stale)
+    {
+        uint32_t stride = 8;
+        for (uint32_t g : act)
+            stride = std::max<uint32_t>(stride, c->h_tcoarse[g].cls_end[3]);
+        std::vector<uint2> offs((size_t)act.size() * stride, make_uint2(0u, 0u));
+        for (size_t i = 0; i < act.size(); ++i)
+            decodeOffsets(c, act[i], offs.data() + i * stride);
+        if (c->sim_offs_cap < offs.size() || !c->d_sim_offs)
+        {
+            freeDev(c->d_sim_offs);
+            c->sim_offs_cap = std::max<size_t>(8, offs.size());
+            CK(cudaMalloc(&c->d_sim_offs, c->sim_offs_cap * sizeof(uint2)));
+            realloc = true;
+        }
+        if (!offs.empty())
+            CK(cudaMemcpy(c->d_sim_offs, offs.data(), offs.size() * sizeof(uint2), cudaMemcpyHostToDevice));
+        if (stride != c->sim_stride)
+            realloc = true; // the stride is a kernel argument baked into the graphs
+        c->sim_stride = stride;
+    }
     std::vector<SimItem> items(act.size());
     for (size_t i = 0; i < act.size(); ++i)
         items[i] = makeSimItem(c, act[i], threshold);
-    CK(cudaDeviceSynchronize()); // frames in flight may still read the previous records
     if (c->sim_items_cap < items.size() || !c->d_sim_items)
     {
         freeDev(c->d_sim_items);
         c->sim_items_cap = (uint32_t)std::max<size_t>(1, items.size());
         CK(cudaMalloc(&c->d_sim_items, c->sim_items_cap * sizeof(SimItem)));
-        ++c->epoch; // the pointer is baked into the slots' graphs
+        realloc = true;
     }
     if (!items.empty())
         CK(cudaMemcpy(c->d_sim_items, items.data(), items.size() * sizeof(SimItem), cudaMemcpyHostToDevice));
-    c->sim_epoch = c->epoch;
+    if (realloc)
+        ++c->epoch; // pointers / stride are baked into the slots' graphs
+    c->sim_epoch = c->sim_offs_epoch = c->epoch;
     c->sim_threshold = threshold;
     return 0;
 }
@@ -748,6 +809,8 @@ struct CoarseLaunch
     const uint32_t *coff, *active;
     const TemplCoarse *tc;
     const SimItem *items;
+    const uint2 *offs;
+    uint32_t stride;
     int W, HW, T;
     float threshold;
     Cand *out;
@@ -757,18 +820,34 @@ struct CoarseLaunch
     void *argv[12];
 };
 
-void makeCoarse(CoarseLaunch &L, const sbm_ctx *c, const uint8_t *lm, const SimItem *items, const uint32_t *active, uint32_t n_active, float threshold,
-                Cand *out, uint32_t *counter, uint32_t cap, uint16_t *dump)
+// items / offs: NULL = the context's active list (ensureSimItems); else one-off arrays with their own stride
+void makeCoarse(CoarseLaunch &L, const sbm_ctx *c, const uint8_t *lm, const SimItem *items, const uint2 *offs, uint32_t stride, const uint32_t *active,
+                uint32_t n_active, float threshold, Cand *out, uint32_t *counter, uint32_t cap, uint16_t *dump)
 {
     const LevelGeom &CG = c->geom[c->levels - 1];
-    L.lm = lm, L.coff = c->d_coff, L.active = active, L.tc = c->d_tcoarse, L.items = items ? items : c->d_sim_items;
+    // (the bit-plane kernel addresses from the start of the allocation: its staged offsets carry K5B_FRONT)
+    L.lm = CG.bits ? lm - K5B_FRONT : lm, L.coff = c->d_coff, L.active = active, L.tc = c->d_tcoarse, L.items = items ? items : c->d_sim_items;
+    L.offs = items ? offs : c->d_sim_offs, L.stride = items ? stride : c->sim_stride;
     L.W = CG.W, L.HW = CG.W * CG.H, L.T = CG.T, L.threshold = threshold, L.out = out, L.counter = counter, L.cap = cap, L.dump = dump;
     if (CG.bits)
     {
         // counter planes: 127 features fit 7 planes, 1023 fit 10, 8191 fit 13
-        L.func = c->max_coarse_valid <= 127 ? (void *)k_similarity_bits<3> : c->max_coarse_valid <= 1023 ? (void *)k_similarity_bits<6> : (void *)k_similarity_bits<9>;
-        L.grid = dim3(n_active, (L.HW + K5B_TILE - 1) / K5B_TILE), L.block = dim3(K5B_THREADS);
-        void *a[] = {&L.lm, &L.coff, &L.items, &L.W, &L.HW, &L.T, &L.out, &L.counter, &L.cap, &L.dump};
+        const int nh = c->max_coarse_valid <= 127 ? 0 : c->max_coarse_valid <= 1023 ? 1 : 2;
+        L.grid = dim3(n_active, (L.HW + K5B_TILE - 1) / K5B_TILE);
+        // few (template, tile) pairs leave the SMs empty: split each tile's features over K warp pairs, K as large as
+        // still lets the whole grid be resident at once (sbm_create asked the occupancy calculator)
+        const long ctas = (long)L.grid.x * L.grid.y;
+        int K = 1;
+        for (int k = 2; k <= K5B_SPLIT_MAX; ++k)
+            if (ctas * 2 * (k - 1) < 4L * 4 * c->sms && ctas <= (long)c->sms * c->bits_split_ctas[nh][k])
+                K = k;
+        if (const char *ev = getenv("SBM_BITS_SPLIT"))
+            K = std::max(1, std::min(K5B_SPLIT_MAX, atoi(ev)));
+        static void *const plain[3] = {(void *)k_similarity_bits<3, false>, (void *)k_similarity_bits<6, false>, (void *)k_similarity_bits<9, false>};
+        static void *const split[3] = {(void *)k_similarity_bits<3, true>, (void *)k_similarity_bits<6, true>, (void *)k_similarity_bits<9, true>};
+        L.func = K > 1 ? split[nh] : plain[nh];
+        L.block = dim3(K5B_THREADS * K);
+        void *a[] = {&L.lm, &L.offs, &L.stride, &L.items, &L.W, &L.HW, &L.T, &L.out, &L.counter, &L.cap, &L.dump};
         memcpy(L.argv, a, sizeof(a));
     }
     else
@@ -780,11 +859,11 @@ void makeCoarse(CoarseLaunch &L, const sbm_ctx *c, const uint8_t *lm, const SimI
     }
 }
 
-cudaError_t launchCoarse(const sbm_ctx *c, const uint8_t *lm, const SimItem *items, const uint32_t *active, uint32_t n_active, float threshold, Cand *out,
-                         uint32_t *counter, uint32_t cap, uint16_t *dump, cudaStream_t st)
+cudaError_t launchCoarse(const sbm_ctx *c, const uint8_t *lm, const SimItem *items, const uint2 *offs, uint32_t stride, const uint32_t *active,
+                         uint32_t n_active, float threshold, Cand *out, uint32_t *counter, uint32_t cap, uint16_t *dump, cudaStream_t st)
 {
     CoarseLaunch L;
-    makeCoarse(L, c, lm, items, active, n_active, threshold, out, counter, cap, dump);
+    makeCoarse(L, c, lm, items, offs, stride, active, n_active, threshold, out, counter, cap, dump);
     return cudaLaunchKernel(L.func, L.grid, L.block, L.argv, 0, st);
 }
 
@@ -833,7 +912,7 @@ int enqueueFrame(sbm_ctx *c, Slot &s, const uint8_t *d_img, const uint8_t *d_mas
     uint32_t *out_cnt = (L == 1 && user_count) ? user_count : s.d_counts + 0;
     if (c->n_active > 0)
     {
-        CK(launchCoarse(c, s.lv[L - 1].d_lm, nullptr, c->d_active, c->n_active, threshold, out, out_cnt, out_cap, nullptr, st));
+        CK(launchCoarse(c, s.lv[L - 1].d_lm, nullptr, nullptr, 0, c->d_active, c->n_active, threshold, out, out_cnt, out_cap, nullptr, st));
         ++launches;
     }
     if (c->timing)
@@ -1009,7 +1088,7 @@ int buildGraph(sbm_ctx *c, Slot &s, const uint8_t *src0, float threshold, bool w
     if (c->n_active > 0)
     {
         CoarseLaunch CL;
-        makeCoarse(CL, c, s.lv[L - 1].d_lm, nullptr, c->d_active, c->n_active, threshold, in, in_cnt, in_cap, nullptr);
+        makeCoarse(CL, c, s.lv[L - 1].d_lm, nullptr, nullptr, 0, c->d_active, c->n_active, threshold, in, in_cnt, in_cap, nullptr);
         cudaGraphNode_t n_sim;
         {
             const cudaGraphNode_t deps[2] = {n_memset, spread_node[L - 1]};
@@ -1049,6 +1128,7 @@ int buildGraph(sbm_ctx *c, Slot &s, const uint8_t *src0, float threshold, bool w
     s.d_final = in;
     s.d_final_count = in_cnt;
     s.final_cap = in_cap;
+    s.graph_final = in, s.graph_final_count = in_cnt, s.graph_final_cap = in_cap;
     if (with_fetch)
     {
         // tail depends on every other node transitively except possibly finer-level spreads when n_active == 0
@@ -1109,6 +1189,9 @@ int launchFrameGraph(sbm_ctx *c, Slot &s, const uint8_t *d_img, float threshold,
         s.graph_src0 = d_img;
     }
     CK(cudaGraphLaunch(s.gexec, st));
+    // where THIS graph leaves the frame's records (an eager frame in between -- mask, debug, timing -- may have pointed
+    // the slot at the caller's own buffers)
+    s.d_final = s.graph_final, s.d_final_count = s.graph_final_count, s.final_cap = s.graph_final_cap;
     s.launches = s.graph_launches;
     s.last_src0 = d_img;
     s.have_frame = true;
@@ -1724,6 +1807,12 @@ int sbm_create(const int *T, int levels, float weak, float strong, int num_featu
         c->sms = 148;
     c->refine_grid[0] = computeRefineGrid(c->sms, false);
     c->refine_grid[1] = computeRefineGrid(c->sms, true);
+    for (int k = 2; k <= K5B_SPLIT_MAX; ++k)
+    {
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c->bits_split_ctas[0][k], k_similarity_bits<3, true>, K5B_THREADS * k, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c->bits_split_ctas[1][k], k_similarity_bits<6, true>, K5B_THREADS * k, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c->bits_split_ctas[2][k], k_similarity_bits<9, true>, K5B_THREADS * k, 0);
+    }
     c->T.assign(T, T + levels);
     c->levels = levels;
     c->weak = weak, c->strong = strong, c->num_features = num_features;
@@ -1750,6 +1839,7 @@ int sbm_destroy(sbm_ctx *c)
     freeDev(c->d_coff);
     freeDev(c->d_active);
     freeDev(c->d_sim_items);
+    freeDev(c->d_sim_offs);
     delete c;
     return 0;
 }
@@ -2270,16 +2360,23 @@ int sbm_similarity_map(sbm_ctx *c, int class_idx, int template_id, uint16_t *dst
     CK(cudaMemcpy(d_one, &gid, 4, cudaMemcpyHostToDevice));
     CK(cudaMemset(d_cnt, 0, 4));
     SimItem *d_item = nullptr;
-    if (CG.bits) // the bit-plane kernel takes one record per template instead of (active[], tinfo[])
+    uint2 *d_offs = nullptr;
+    uint32_t stride = 8;
+    if (CG.bits) // the bit-plane kernel takes one record and one offset row per template instead of (active[], tinfo[])
     {
         const SimItem it = makeSimItem(c, gid, 1e30f);
+        stride = std::max<uint32_t>(8, it.n_off);
+        std::vector<uint2> offs(stride, make_uint2(0u, 0u));
+        decodeOffsets(c, gid, offs.data());
         CK(cudaMalloc(&d_item, sizeof(SimItem)));
+        CK(cudaMalloc(&d_offs, stride * sizeof(uint2)));
         CK(cudaMemcpy(d_item, &it, sizeof(SimItem), cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(d_offs, offs.data(), stride * sizeof(uint2), cudaMemcpyHostToDevice));
     }
-    CK(launchCoarse(c, s.lv[c->levels - 1].d_lm, d_item, d_one, 1, 1e30f, d_sink, d_cnt, 0, d_dump, s.stream));
+    CK(launchCoarse(c, s.lv[c->levels - 1].d_lm, d_item, d_offs, stride, d_one, 1, 1e30f, d_sink, d_cnt, 0, d_dump, s.stream));
     CK(cudaStreamSynchronize(s.stream));
     CK(cudaMemcpy(dst, d_dump, (size_t)HW * 2, cudaMemcpyDeviceToHost));
-    cudaFree(d_one), cudaFree(d_cnt), cudaFree(d_sink), cudaFree(d_dump), cudaFree(d_item);
+    cudaFree(d_one), cudaFree(d_cnt), cudaFree(d_sink), cudaFree(d_dump), cudaFree(d_item), cudaFree(d_offs);
     return 0;
 }
 
@@ -2384,7 +2481,7 @@ int sbm_time_similarity(sbm_ctx *c, float threshold, int iters, float *ms_per_la
     CK(cudaStreamBeginCapture(s.stream, cudaStreamCaptureModeThreadLocal));
     for (int i = 0; i < iters; ++i)
         // same launch as the pipeline's; the candidate counter keeps running, records beyond cap are dropped
-        CK(launchCoarse(c, s.lv[L - 1].d_lm, nullptr, c->d_active, c->n_active, threshold, s.d_buf[1], s.d_counts + 12, 0u, nullptr, s.stream));
+        CK(launchCoarse(c, s.lv[L - 1].d_lm, nullptr, nullptr, 0, c->d_active, c->n_active, threshold, s.d_buf[1], s.d_counts + 12, 0u, nullptr, s.stream));
     CK(cudaStreamEndCapture(s.stream, &tg));
     CK(cudaGraphInstantiate(&te, tg, 0));
     CK(cudaGraphLaunch(te, s.stream));
@@ -2508,7 +2605,7 @@ int sbm_time_kernels(sbm_ctx *c, float threshold, int iters, float *ms, int n_ms
     uint32_t *d_tmp = nullptr;
     CK(cudaMalloc(&d_tmp, COUNT_WORDS * 4));
     CK(cudaMemsetAsync(d_tmp, 0, COUNT_WORDS * 4, st));
-    SBM_TIME(3 * L, (void)launchCoarse(c, s.lv[L - 1].d_lm, nullptr, c->d_active, c->n_active, threshold, s.d_buf[1], d_tmp, 0u, nullptr, st));
+    SBM_TIME(3 * L, (void)launchCoarse(c, s.lv[L - 1].d_lm, nullptr, nullptr, 0, c->d_active, c->n_active, threshold, s.d_buf[1], d_tmp, 0u, nullptr, st));
     // refinement of the frame's own coarse candidates (stage counts of the last real run), output discarded
     int stage = 1;
     for (int l = L - 2; l >= 0; --l, ++stage)
