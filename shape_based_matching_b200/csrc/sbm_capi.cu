@@ -566,9 +566,8 @@ int ensureTemplates(sbm_ctx *c)
                                          (uint32_t)(f.y / T) * W + (uint32_t)(f.x / T);
                             // k_similarity_nib has two shift classes (bit 3 of the offset): buckets 1 and 3 only, half the padding
                             // k_similarity_bits: the parity of the stream's first word pair (bit 5), buckets 1 and 3 as well
-                            // (a stream that starts on a word boundary is staged one pair earlier, see decodeOffsets)
-                            const uint32_t pair0 = (a >> 5) - ((a & 31u) == 0 ? 1u : 0u);
-                            cls[G.bits ? (pair0 & 1) * 2 + 1 : G.nib ? ((a >> 3) & 1) * 2 + 1 : (a >> 2) & 3].push_back(a);
+                            // k_similarity_bits shifts by off & 31 whatever it is: one bucket (3), padded once
+                            cls[G.bits ? 3 : G.nib ? ((a >> 3) & 1) * 2 + 1 : (a >> 2) & 3].push_back(a);
                         }
                         int nv = 0, stored = 0;
                         for (int k = 0; k < 4; ++k)
@@ -577,7 +576,7 @@ int ensureTemplates(sbm_ctx *c)
                             // pad with reads of the zeroed tail (same word shift): adds 0, keeps batches full
                             // (bit planes: the zero words behind the memories, first pair even for bucket 1, odd for bucket 3)
                             // (bit planes: the zero words behind the memories, first pair even for bucket 1, odd for bucket 3)
-                            const uint32_t zero_off = G.bits ? (uint32_t)((G.lm_bytes + 63) / 64 * 64) + (k == 3 ? 33u : 1u) : (uint32_t)G.lm_bytes + 4u * k;
+                            const uint32_t zero_off = G.bits ? (uint32_t)((G.lm_bytes + 63) / 64 * 64) : (uint32_t)G.lm_bytes + 4u * k;
                             while (cls[k].size() % K5_U)
                                 cls[k].push_back(zero_off);
                             off.insert(off.end(), cls[k].begin(), cls[k].end());
@@ -708,7 +707,6 @@ SimItem makeSimItem(const sbm_ctx *c, uint32_t gid, float threshold)
     it.nf = t.nf;
     it.tp = t.tp;
     it.rawmin = minPassingRawHost(t.nf, threshold);
-    it.n_even = t.cls_end[1];
     it.n_off = t.cls_end[3];
     return it;
 }
@@ -719,14 +717,9 @@ void decodeOffsets(const sbm_ctx *c, uint32_t gid, uint2 *dst)
     const TemplCoarse &t = c->h_tcoarse[gid];
     for (int i = 0; i < (int)t.cls_end[3]; ++i)
     {
-        // stream of position j = bit (o + j) of the flat bit sequence: first pair k = o >> 5, shift s = o & 31; a shift of
-        // 0 is staged as (k - 1, 32) so that the multiplier 2^(32 - s) fits 32 bits (k5b_funnel)
+        // stream of position j = bit (o + j) of the flat bit sequence: first pair o >> 5, shift o & 31
         const uint32_t o = c->h_coff[t.off_begin + i];
-        int64_t k = o >> 5;
-        uint32_t sft = o & 31u;
-        if (sft == 0)
-            --k, sft = 32;
-        dst[i] = make_uint2((uint32_t)((int64_t)K5B_FRONT + k * 8), 1u << (32 - sft));
+        dst[i] = make_uint2(K5B_FRONT + (o >> 5) * 8u, o & 31u);
     }
 }
 
@@ -834,12 +827,13 @@ void makeCoarse(CoarseLaunch &L, const sbm_ctx *c, const uint8_t *lm, const SimI
         // counter planes: 127 features fit 7 planes, 1023 fit 10, 8191 fit 13
         const int nh = c->max_coarse_valid <= 127 ? 0 : c->max_coarse_valid <= 1023 ? 1 : 2;
         L.grid = dim3(n_active, (L.HW + K5B_TILE - 1) / K5B_TILE);
-        // few (template, tile) pairs leave the SMs empty: split each tile's features over K warp pairs, K as large as
-        // still lets the whole grid be resident at once (sbm_create asked the occupancy calculator)
+        // What bounds the kernel is issue latency per warp, so small workloads want more warps: split each tile's features
+        // over K warp groups, K the smallest that gives every scheduler three warps, as long as the whole grid still
+        // fits the SMs at once (sbm_create asked the occupancy calculator)
         const long ctas = (long)L.grid.x * L.grid.y;
         int K = 1;
-        for (int k = 2; k <= K5B_SPLIT_MAX; ++k)
-            if (ctas * 2 * (k - 1) < 4L * 4 * c->sms && ctas <= (long)c->sms * c->bits_split_ctas[nh][k])
+        for (int k = 2; k <= K5B_SPLIT_MAX && ctas * (K5B_THREADS / 32) * K < 12L * c->sms; ++k)
+            if (ctas <= (long)c->sms * c->bits_split_ctas[nh][k])
                 K = k;
         if (const char *ev = getenv("SBM_BITS_SPLIT"))
             K = std::max(1, std::min(K5B_SPLIT_MAX, atoi(ev)));
