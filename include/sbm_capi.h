@@ -231,6 +231,11 @@ int sbm_similarity_local(sbm_ctx *ctx, int class_idx, int template_id, int level
 int sbm_quantized_orientations(sbm_ctx *ctx, const uint8_t *img, int w, int h, int channels, size_t stride, int level,
                                float *magnitude, float *angle_ori, uint8_t *angle, uint8_t *src_level, int *w_out, int *h_out);
 
+/* Test tap: cv::phase in degrees (line2Dup.cpp:327, :398) and the 16-bin label hysteresisGradient derives from it (:225,
+ * :249) for n integer Sobel responses (dy[i], dx[i]), computed by the device functions the orientation kernel uses.
+ * Either output may be NULL.  tests/test_gpu_phase.py runs every pair of [-1020, 1020]^2 against the OpenCV restatement. */
+int sbm_phase_degrees(int device, const int *dy, const int *dx, int n, float *angle, uint8_t *label);
+
 /* Counters of the most recent frame: [0] coarse evaluations (sum over matched templates of
  * in-image features * template_positions), [1] coarse candidates, [2] local evaluations,
  * [3] records after refinement, [4] kernels launched by the most recent call, [5] layout of the coarsest level's linear

@@ -2629,6 +2629,32 @@ int sbm_time_kernels(sbm_ctx *c, float threshold, int iters, float *ms, int n_ms
     return 0;
 }
 
+int sbm_phase_degrees(int device, const int *dy, const int *dx, int n, float *angle, uint8_t *label)
+{
+    if (!dy || !dx || n < 0 || (!angle && !label))
+        return fail(SBM_ERR_BAD_ARG, "bad argument");
+    CK(cudaSetDevice(device));
+    struct DevBuf
+    {
+        void *p = nullptr;
+        ~DevBuf() { cudaFree(p); }
+    } d_y, d_x, d_a, d_l;
+    const size_t nb = (size_t)std::max(n, 1) * 4;
+    CK(cudaMalloc(&d_y.p, nb));
+    CK(cudaMalloc(&d_x.p, nb));
+    CK(cudaMalloc(&d_a.p, nb));
+    CK(cudaMalloc(&d_l.p, (size_t)std::max(n, 1)));
+    CK(cudaMemcpy(d_y.p, dy, (size_t)n * 4, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(d_x.p, dx, (size_t)n * 4, cudaMemcpyHostToDevice));
+    k_phase_tap<<<148 * 8, 256>>>((const int *)d_y.p, (const int *)d_x.p, n, (float *)d_a.p, (uint8_t *)d_l.p);
+    CK(cudaGetLastError());
+    if (angle)
+        CK(cudaMemcpy(angle, d_a.p, (size_t)n * 4, cudaMemcpyDeviceToHost));
+    if (label)
+        CK(cudaMemcpy(label, d_l.p, (size_t)n, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
 int sbm_quantized_orientations(sbm_ctx *c, const uint8_t *img, int w, int h, int ch, size_t stride, int level, float *magnitude,
                                float *angle_ori, uint8_t *angle, uint8_t *src_level, int *w_out, int *h_out)
 {
