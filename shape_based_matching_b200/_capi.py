@@ -89,6 +89,26 @@ def lib():
     return _lib
 
 
+def prefer_bundled_nccl():
+    """Before the first sbm_group_* call of a Python process: point the library's run-time NCCL binding (SBM_NCCL_LIB)
+    at the libnccl.so.2 this Python environment ships (the nvidia-nccl wheel torch links against), if there is one and the
+    caller has not chosen.  The C library by itself takes the copy already mapped into the process, else the system's --
+    and a system NCCL older than torch's, loaded first under the same soname, would break a later `import torch`."""
+    if os.environ.get("SBM_NCCL_LIB"):
+        return
+    try:
+        import importlib.util
+
+        spec = importlib.util.find_spec("nvidia.nccl")
+        for base in (spec.submodule_search_locations if spec else []):
+            cand = os.path.join(base, "lib", "libnccl.so.2")
+            if os.path.exists(cand):
+                os.environ["SBM_NCCL_LIB"] = cand
+                return
+    except Exception:
+        pass
+
+
 def check(rc):
     if rc < 0:
         raise SbmError(rc, lib().sbm_last_error().decode())

@@ -297,6 +297,7 @@ class Detector:
     @staticmethod
     def group_unique_id():
         """128 bytes from rank 0 (ncclGetUniqueId) that every rank hands to group_create"""
+        _capi.prefer_bundled_nccl()
         buf = C.create_string_buffer(_capi.GROUP_ID_BYTES)
         check(_capi.lib().sbm_group_unique_id(buf))
         return buf.raw
@@ -305,6 +306,7 @@ class Detector:
         """join a group of n_ranks detectors (collective).  Template modes: keep calling setClassTemplates with the
         FULL classes on every rank, the context keeps this rank's slice."""
         assert len(unique_id) == _capi.GROUP_ID_BYTES
+        _capi.prefer_bundled_nccl()
         check(self._L.sbm_clear_templates(self._h))
         self._dirty = True
         check(self._L.sbm_group_create(self._h, int(n_ranks), int(rank), C.c_char_p(unique_id), int(mode)))

@@ -131,12 +131,18 @@ class CxxDetector:
 
     @staticmethod
     def groupUniqueId():
+        from . import _capi
+
+        _capi.prefer_bundled_nccl()
         buf = C.create_string_buffer(128)
         if lib().l2d_group_unique_id(buf) < 0:
             raise RuntimeError(lib().l2d_last_error().decode())
         return buf.raw
 
     def setGroup(self, n_ranks, rank, unique_id, mode=0):
+        from . import _capi
+
+        _capi.prefer_bundled_nccl()
         self._chk(self.L.l2d_set_group(self.h, int(n_ranks), int(rank), C.c_char_p(unique_id), int(mode)))
 
 
