@@ -1003,7 +1003,7 @@ cudaError_t launchSpread(const LevelGeom &G, const uint8_t *quant, uint8_t *lm, 
     dim3 g2((G.w + K2_PW - 1) / K2_PW, (G.h + K2_PH - 1) / K2_PH);
     int w = G.w, h = G.h;
     void *argv[] = {(void *)&quant, (void *)&w, (void *)&h, (void *)&lm, (void *)&dbg_spread, (void *)&dbg_resp};
-    return cudaLaunchKernel(spreadFunc(G.T, G.nib, G.tiled, G.bits), g2, dim3(K2_THREADS), argv, 0, st);
+    return cudaLaunchKernel(spreadFunc(G.T, G.nib, G.tiled, G.bits), g2, dim3(G.bits ? K2_THREADS_BITS : K2_THREADS), argv, 0, st);
 }
 
 int buildGraph(sbm_ctx *c, Slot &s, const uint8_t *src0, float threshold, bool with_fetch)
@@ -1067,7 +1067,7 @@ int buildGraph(sbm_ctx *c, Slot &s, const uint8_t *src0, float threshold, bool w
             s.n_orient0 = n_or, s.f_orient0 = orientFunc(c->c, th), s.g_orient0 = g1;
         dim3 g2((G.w + K2_PW - 1) / K2_PW, (G.h + K2_PH - 1) / K2_PH);
         const uint8_t *qin = LB.d_quant;
-        if ((rc = addKernel(g, &n_sp, {n_or}, spreadFunc(G.T, G.nib, G.tiled, G.bits), g2, dim3(K2_THREADS), qin, G.w, G.h, LB.d_lm, null_dbg, null_dbg)))
+        if ((rc = addKernel(g, &n_sp, {n_or}, spreadFunc(G.T, G.nib, G.tiled, G.bits), g2, dim3(G.bits ? K2_THREADS_BITS : K2_THREADS), qin, G.w, G.h, LB.d_lm, null_dbg, null_dbg)))
             return rc;
         spread_node[l] = n_sp;
         launches += 2;
