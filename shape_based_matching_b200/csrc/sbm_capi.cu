@@ -2744,3 +2744,10 @@ extern "C" int sbm_trace_read(unsigned long long *out16, int reset)
     return 0;
 }
 #endif
+
+#ifdef K5B_TRACE // experiments only (tools/sim_trace.py)
+extern "C" int sbm_debug_k5b_trace(long long *out16)
+{
+    return (int)cudaMemcpyFromSymbol(out16, sbm::g_k5b_trace, 16 * sizeof(long long));
+}
+#endif

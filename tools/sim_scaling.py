@@ -1,26 +1,37 @@
-"""similarity_ms (CUDA events around k_similarity) as a function of the number of templates: separates the fixed
-cost (launch + prologue latency) from the marginal cost per template."""
+"""Coarse similarity kernel alone (50 launches in one graph) against the number of active templates, M1 frame:
+is it one CTA's latency (flat) or throughput (linear)?   python tools/sim_scaling.py [lib.so] [K=V ...]"""
+import os
 import sys
-sys.path.insert(0, "tests"); sys.path.insert(0, ".")
-import numpy as np, torch
-from _fixtures import load_case, load_templates
-from shape_based_matching_b200 import Detector
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, ROOT)
+args = sys.argv[1:]
+for a in list(args):
+    if "=" in a and not a.endswith(".so"):
+        k, v = a.split("=", 1)
+        os.environ[k] = v
+        args.remove(a)
+import numpy as np  # noqa: E402
+
+import shape_based_matching_b200._capi as capi  # noqa: E402
+from _fixtures import load_case, load_templates  # noqa: E402
+
+if args:
+    capi.LIB_PATH = os.path.abspath(args[0])
+from shape_based_matching_b200 import Detector  # noqa: E402
+
 case = load_case("m1")
 cid, tdesc, feats, nf = load_templates("case1[:360]")
-d = torch.from_numpy(case["img"]).cuda()
-for reps in (0, 1, 2, 4, 8):
+out = []
+for n in (37, 74, 148, 222, 296, 360, 444, 592, 720, 1080, 1440):
+    reps = (n + 359) // 360
+    td = np.concatenate([tdesc] * reps)[:n]
+    ft = np.concatenate([feats] * reps)[: int(td[:, :, 4].sum())]
     det = Detector(nf, (4, 8))
-    if reps == 0:
-        n1 = int(tdesc[:1, :, 4].sum())
-        det.setClassTemplates("c0", tdesc[:1], feats[:n1])
-    for r in range(reps):
-        det.setClassTemplates("c%d" % r, tdesc, feats)
-    det.set_timing(True)
-    ts = []
-    for i in range(40):
-        det.match_device(d.data_ptr(), 1024, 1024, 3, 90.0)
-        torch.cuda.synchronize()
-        ts.append(det.last_timing())
-    med = {k: float(np.median([t[k] for t in ts[5:]])) for k in ts[0]}
-    print("templates=%4d" % max(1, 360 * reps), {k: round(v * 1e3, 1) for k, v in med.items()}, "us")
+    det.setClassTemplates(cid, td, ft)
+    det.match_records(case["img"], 90.0, [cid])
+    us = min(det.time_similarity(90.0, 50) for _ in range(3)) * 1e3
+    out.append("%d: %.2f" % (n, us))
     det.close()
+print({k: v for k, v in os.environ.items() if k.startswith("SBM_")}, "templates: us |", "  ".join(out))
