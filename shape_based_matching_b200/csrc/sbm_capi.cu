@@ -247,6 +247,11 @@ struct sbm_ctx
         uint8_t *h_recv = nullptr; // pinned copy of d_recv
         size_t h_alloc = 0;
         uint32_t cap = 256; // records per frame block of the host-side group calls (grown on overflow)
+        // host-side group calls: the exchange + D2H of a chunk of frames run on their own stream while the next chunk
+        // uploads, and the host orders chunk k's lists meanwhile
+        cudaStream_t xstream = nullptr;
+        std::vector<cudaEvent_t> chunk_done;
+        std::vector<sbm_match_rec> pool; // final records of the chunks, before they are laid out list by list
     } group;
 };
 
@@ -1523,6 +1528,10 @@ void destroyGroup(sbm_ctx *c)
     freeDev(G.d_recv);
     if (G.h_recv)
         cudaFreeHost(G.h_recv);
+    for (cudaEvent_t e : G.chunk_done)
+        cudaEventDestroy(e);
+    if (G.xstream)
+        cudaStreamDestroy(G.xstream);
     if (G.mode != SBM_GROUP_FRAMES) // the context holds a slice of every class: meaningless without the group
     {
         c->classes.clear();
@@ -1567,9 +1576,12 @@ int ensureGroupBuffers(sbm_ctx *c, size_t send_bytes, bool own_recv)
 
 // Enqueue n_frames frames (host pointers `imgs`, or resident at d_imgs + i * frame_stride) over the frame slots with their
 // results exported into the send blocks, join the slot streams on `user`, and allgather the blocks into d_gathered on `user`.
+// A caller that feeds a batch in chunks passes the chunk's position (`first` of `total` frames): the chunk's send blocks
+// and slots continue where the previous chunk stopped, so chunks in flight never share memory; wait_user = false when
+// nothing queued on `user` has to finish before the frames may start.
 int groupEnqueue(sbm_ctx *c, const uint8_t *const *imgs, const uint8_t *const *masks, const void *d_imgs, size_t frame_stride, int n_frames,
                  int w, int h, int ch, size_t stride, float threshold, const int *class_idx, int n_classes, uint32_t cap, uint8_t *d_gathered,
-                 cudaStream_t user)
+                 cudaStream_t user, int first = 0, int total = -1, bool wait_user = true)
 {
     sbm_ctx::Group &G = c->group;
     NcclApi *N = NcclApi::get();
@@ -1577,17 +1589,19 @@ int groupEnqueue(sbm_ctx *c, const uint8_t *const *imgs, const uint8_t *const *m
         return fail(SBM_ERR_STATE, "no group: call sbm_group_create first");
     int rc;
     const int NS = frameSlots();
-    const int ns = std::min(n_frames, NS);
+    if (total < 0)
+        total = n_frames;
+    const int ns = std::min(total, NS); // (a chunk of a longer batch may wrap around the slots)
     for (int k = 0; k < ns; ++k)
         if ((rc = prepare(c, c->slot[k], w, h, ch, class_idx, n_classes, threshold)))
             return rc;
     const size_t blk = groupBlockBytes(cap);
-    if ((rc = ensureGroupBuffers(c, blk * n_frames, d_gathered == nullptr)))
+    if ((rc = ensureGroupBuffers(c, blk * total, d_gathered == nullptr)))
         return rc;
     if (!d_gathered)
         d_gathered = G.d_recv;
     Slot &s0 = c->slot[0];
-    if (ns > 0)
+    if (ns > 0 && wait_user)
     {
         CK(cudaEventRecord(s0.ev[0], user));
         for (int k = 0; k < ns; ++k)
@@ -1596,10 +1610,11 @@ int groupEnqueue(sbm_ctx *c, const uint8_t *const *imgs, const uint8_t *const *m
     const bool timing = c->timing, debug = c->debug;
     c->timing = false, c->debug = false;
     rc = 0;
+    uint8_t *const send = G.d_send + (size_t)first * blk;
     for (int i = 0; i < n_frames && !rc; ++i)
     {
-        Slot &s = c->slot[i % NS];
-        uint8_t *block = G.d_send + (size_t)i * blk;
+        Slot &s = c->slot[(first + i) % NS];
+        uint8_t *block = send + (size_t)i * blk;
         const uint8_t *img = nullptr, *dm = nullptr;
         if (imgs)
         {
@@ -1617,14 +1632,15 @@ int groupEnqueue(sbm_ctx *c, const uint8_t *const *imgs, const uint8_t *const *m
     c->timing = timing, c->debug = debug;
     if (rc)
         return rc;
-    for (int k = 0; k < ns; ++k)
+    for (int k = 0; k < std::min(ns, n_frames); ++k)
     {
-        CK(cudaEventRecord(c->slot[k].ev[1], c->slot[k].stream));
-        CK(cudaStreamWaitEvent(user, c->slot[k].ev[1], 0));
+        Slot &s = c->slot[(first + k) % NS];
+        CK(cudaEventRecord(s.ev[1], s.stream));
+        CK(cudaStreamWaitEvent(user, s.ev[1], 0));
     }
     if (n_frames > 0)
     {
-        const int r = N->AllGather(G.d_send, d_gathered, blk * n_frames, NcclApi::kUint8, G.comm, user);
+        const int r = N->AllGather(send, d_gathered, blk * n_frames, NcclApi::kUint8, G.comm, user);
         if (r)
             return ncclFail(N, r, "ncclAllGather");
     }
@@ -1727,28 +1743,109 @@ int groupFinalize(sbm_ctx *c, const uint8_t *h, int n_frames, uint32_t cap, cons
     return 0;
 }
 
-// host frames -> final host lists through the group (see sbm_group_match_batch)
+// frames per chunk of the host-side group calls (SBM_GROUP_CHUNK; at least one round of the frame slots)
+int groupChunk()
+{
+    static const int v = [] {
+        const char *e = getenv("SBM_GROUP_CHUNK");
+        return std::max(frameSlots(), e ? atoi(e) : 32);
+    }();
+    return v;
+}
+
+// host frames -> final host lists through the group (see sbm_group_match_batch).  The batch goes through in chunks:
+// chunk k's frames upload and run on the frame slots, its blocks are exchanged and copied to the host on the group's
+// own stream, and while chunk k+1 is on its way the host orders chunk k's lists (with n ranks that is n times the
+// host work of a single GPU, and it would otherwise sit behind the last copy).
 int groupMatchHost(sbm_ctx *c, const uint8_t *const *imgs, const uint8_t *const *masks, int n_frames, int w, int h, int ch, size_t stride,
                    float threshold, const int *class_idx, int n_classes, bool finalize, sbm_match_rec *out, int cap, int *frame_begin)
 {
     sbm_ctx::Group &G = c->group;
     int rc;
+    const int CH = groupChunk(), n_chunks = (n_frames + CH - 1) / CH;
+    const int per_frame = G.mode == SBM_GROUP_FRAMES ? G.n : 1, lists = n_frames * per_frame;
+    if (!G.xstream)
+        CK(cudaStreamCreateWithFlags(&G.xstream, cudaStreamNonBlocking));
+    while ((int)G.chunk_done.size() < n_chunks)
+    {
+        cudaEvent_t e;
+        CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        G.chunk_done.push_back(e);
+    }
+    std::vector<size_t> pos(lists);
+    std::vector<int> cnt(lists), fb;
     for (int attempt = 0; attempt < 8; ++attempt)
     {
-        if ((rc = ensureStream(c->slot[0])))
+        const size_t blk = groupBlockBytes(G.cap);
+        if ((rc = ensureGroupBuffers(c, blk * n_frames, true)))
             return rc;
-        cudaStream_t st = c->slot[0].stream;
-        if ((rc = groupEnqueue(c, imgs, masks, nullptr, 0, n_frames, w, h, ch, stride, threshold, class_idx, n_classes, G.cap, nullptr, st)))
-            return rc;
-        const size_t bytes = groupBlockBytes(G.cap) * n_frames * G.n;
-        CK(cudaMemcpyAsync(G.h_recv, G.d_recv, bytes, cudaMemcpyDeviceToHost, st));
-        CK(cudaStreamSynchronize(st));
         uint32_t worst = 0;
         bool overflow = false;
-        if ((rc = groupFinalize(c, G.h_recv, n_frames, G.cap, class_idx, n_classes, finalize, out, cap, frame_begin, &worst, &overflow)))
+        size_t pool_used = 0;
+        // the lists of chunk k: wait for its copy, order them into the pool, remember where each global list lies
+        auto finish_chunk = [&](int k) -> int {
+            const int c0 = k * CH, cn = std::min(CH, n_frames - c0);
+            CK(cudaEventSynchronize(G.chunk_done[k]));
+            const size_t need = (size_t)G.n * cn * G.cap;
+            if (G.pool.size() < pool_used + need)
+                G.pool.resize(std::max(pool_used + need, 2 * G.pool.size()));
+            fb.assign((size_t)cn * per_frame + 1, 0);
+            uint32_t wk = 0;
+            bool ov = false;
+            const int r = groupFinalize(c, G.h_recv + (size_t)G.n * blk * c0, cn, G.cap, class_idx, n_classes, finalize, G.pool.data() + pool_used,
+                                        (int)std::min<size_t>(need, 0x7fffffff), fb.data(), &wk, &ov);
+            if (r)
+                return r;
+            worst = std::max(worst, wk);
+            if (ov)
+            {
+                overflow = true;
+                return 0;
+            }
+            for (int j = 0; j < cn * per_frame; ++j)
+            {
+                // frame mode: chunk lists are rank-major within the chunk; the batch's are rank-major over all frames
+                const int g = G.mode == SBM_GROUP_FRAMES ? (j / cn) * n_frames + c0 + j % cn : c0 + j;
+                pos[g] = pool_used + fb[j], cnt[g] = fb[j + 1] - fb[j];
+            }
+            pool_used += fb[(size_t)cn * per_frame];
+            return 0;
+        };
+        for (int k = 0; k < n_chunks; ++k)
+        {
+            const int c0 = k * CH, cn = std::min(CH, n_frames - c0);
+            uint8_t *d_dst = G.d_recv + (size_t)G.n * blk * c0;
+            if ((rc = groupEnqueue(c, imgs + c0, masks ? masks + c0 : nullptr, nullptr, 0, cn, w, h, ch, stride, threshold, class_idx, n_classes, G.cap,
+                                   d_dst, G.xstream, c0, n_frames, false)))
+                return rc;
+            CK(cudaMemcpyAsync(G.h_recv + (size_t)G.n * blk * c0, d_dst, (size_t)G.n * blk * cn, cudaMemcpyDeviceToHost, G.xstream));
+            CK(cudaEventRecord(G.chunk_done[k], G.xstream));
+            if (k > 0 && (rc = finish_chunk(k - 1)))
+                return rc;
+        }
+        if (n_chunks > 0 && (rc = finish_chunk(n_chunks - 1)))
             return rc;
         if (!overflow)
+        {
+            int used = 0;
+            bool full = false;
+            frame_begin[0] = 0;
+            for (int g = 0; g < lists; ++g)
+            {
+                if (!full && used + cnt[g] <= cap)
+                {
+                    if (cnt[g] && out)
+                        memcpy(out + used, G.pool.data() + pos[g], (size_t)cnt[g] * sizeof(sbm_match_rec));
+                }
+                else
+                    full = true;
+                used += cnt[g];
+                frame_begin[g + 1] = used;
+            }
+            if (full)
+                return fail(SBM_ERR_CAPACITY, "output holds %d matches, %d needed", cap, used);
             return 0;
+        }
         // every rank sees the same gathered headers, so every rank takes the same decision: larger blocks, larger stage
         // buffers, and the whole batch again (the collective stays matched across the ranks)
         uint32_t nc = G.cap;

@@ -212,7 +212,15 @@ class Detector:
                 cap = begin[lists]
                 continue
             check(rc)
-            return [out[begin[i] : begin[i + 1]].copy() for i in range(lists)]
+            return self._split(out, begin, lists)
+
+    @staticmethod
+    def _split(out, begin, lists):
+        """packed records + list boundaries -> one array per list (views of one trimmed copy: a ctypes int per access and a
+        numpy copy per list would cost more than the C side spends ordering a short list)"""
+        b = np.frombuffer(begin, dtype=np.int32, count=lists + 1).tolist()
+        out = out[: b[lists]].copy()
+        return [out[b[i] : b[i + 1]] for i in range(lists)]
 
     # ---- device-resident path (bench `value`, multi-GPU) ----------------------------------------
     def match_batch_device(self, d_imgs_ptr, frame_stride, n_frames, w, h, channels, threshold, class_ids, d_records, cap_per_frame,
@@ -360,7 +368,7 @@ class Detector:
                 cap = begin[lists]
                 continue
             check(rc)
-            return [out[begin[i] : begin[i + 1]].copy() for i in range(lists)]
+            return self._split(out, begin, lists)
 
     # ---- taps for parity tests ------------------------------------------------------------------
     def set_debug(self, on=True):
