@@ -99,6 +99,36 @@ def test_group_grows_its_blocks():
     det.close()
 
 
+@pytest.mark.parametrize("mode", [0, 2], ids=["templates", "frames"])
+def test_group_batch_longer_than_a_chunk(mode):
+    """the host-side group call feeds a batch in chunks of 32 frames (exchange + host ordering of chunk k overlap chunk
+    k+1): 70 distinct frames = chunks of 32, 32 and 6 must come back in order, equal to one blocking match per frame"""
+    from shape_based_matching_b200 import Detector
+
+    case = load_case("case1")
+    cid, tdesc, feats, nf = load_templates(case["templates"])
+    thr = float(case["threshold"])
+    frames = [np.ascontiguousarray(np.roll(case["img"], (8 * i, 16 * i), axis=(0, 1))) for i in range(70)]
+    single = Detector(nf, [int(t) for t in case["T"]], float(case["weak"]), float(case["strong"]))
+    single.setClassTemplates(cid, tdesc, feats)
+    want = [single.match_records(f, thr, [cid]) for f in frames]
+    single.close()
+    assert len({len(w) for w in want}) > 1  # the frames really differ
+    det = Detector(nf, [int(t) for t in case["T"]], float(case["weak"]), float(case["strong"]))
+    det.group_create(1, 0, Detector.group_unique_id(), mode)
+    det.setClassTemplates(cid, tdesc, feats)
+    for _ in range(2):  # the second pass reuses the chunk events, the pool and the pinned blocks
+        lists = det.group_match_batch(frames, thr, [cid])
+        assert len(lists) == 70
+        for a, b in zip(lists, want):
+            same_list(a, b)
+    # an output buffer that is too small reports the size it needs (the mirror retries with it)
+    lists = det.group_match_batch(frames, thr, [cid], cap=8)
+    for a, b in zip(lists, want):
+        same_list(a, b)
+    det.close()
+
+
 WORKER = r'''
 import os, sys
 import numpy as np
@@ -131,6 +161,23 @@ else:
     assert len(lists) == 2 * world
     for r in range(world):
         same(lists[2 * r + (0 if r %% 2 == 0 else 1)], case["matches"])
+# a batch longer than one chunk of the host-side group call (32 frames): 40 frames per rank, every frame different
+single = Detector(nf, [int(t) for t in case["T"]], float(case["weak"]), float(case["strong"]), device=rank)
+single.setClassTemplates(cid, tdesc, feats)
+def frame(i):
+    return np.ascontiguousarray(np.roll(case["img"], (8 * i, 16 * i), axis=(0, 1)))
+if mode != 2:
+    fr = [frame(i) for i in range(40)]
+    lists = det.group_match_batch(fr, thr, [cid])
+    assert len(lists) == 40
+    for f, l in zip(fr, lists):
+        same(l, single.match_records(f, thr, [cid]))
+else:
+    lists = det.group_match_batch([frame(40 * rank + i) for i in range(40)], thr, [cid])
+    assert len(lists) == 40 * world
+    for r in range(world):
+        for i in range(0, 40, 3):
+            same(lists[40 * r + i], single.match_records(frame(40 * r + i), thr, [cid]))
 print("rank %%d ok" %% rank)
 '''
 
