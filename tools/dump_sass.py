@@ -44,7 +44,11 @@ def main():
                 n += 1
         with open(os.path.join(out_dir, fname), "w") as f:
             f.write("// %s\n// cuobjdump -sass shape_based_matching_b200/libsbm_b200.so at commit %s (+ working tree)\n" % (name, commit))
-            f.write(blk)
+            # instruction text only: the hex encodings (the trailing comment and the continuation line) triple the size
+            for line in blk.split("\n"):
+                if re.match(r"\s+/\* 0x[0-9a-f]+ \*/\s*$", line):
+                    continue
+                f.write(re.sub(r"\s*/\* 0x[0-9a-f]+ \*/\s*$", "", line) + "\n")
         rows.append((short, n, ops))
     with open(os.path.join(out_dir, "SUMMARY.md"), "w") as f:
         f.write("# SASS at %s: static instruction mix per kernel (cuobjdump -sass, sm_100a)\n\n" % commit)
