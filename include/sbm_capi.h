@@ -26,6 +26,7 @@
  *                           of one box: one context per GPU, one ncclAllGather of the compact record lists
  *   sbm_set_candidate_capacity  the `std::vector<Match> candidates` of matchClass (unbounded there)       line2Dup.cpp:1160-1216
  *   sbm_quantized_orientations  quantizedOrientations + hysteresisGradient + pyrDown (training)  line2Dup.cpp:218-444
+ *   sbm_quantized_level1_static  (no counterpart in the reference; operators' request) the same at level 1 without any allocation
  */
 #ifndef SBM_CAPI_H
 #define SBM_CAPI_H
@@ -235,6 +236,23 @@ int sbm_quantized_orientations(sbm_ctx *ctx, const uint8_t *img, int w, int h, i
  * :249) for n integer Sobel responses (dy[i], dx[i]), computed by the device functions the orientation kernel uses.
  * Either output may be NULL.  tests/test_gpu_phase.py runs every pair of [-1020, 1020]^2 against the OpenCV restatement. */
 int sbm_phase_degrees(int device, const int *dy, const int *dx, int n, float *angle, uint8_t *label);
+
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Pyramid level 1 of the training /
+ * matching front end -- cv::pyrDown (cols/2 x rows/2) followed by quantizedOrientations + hysteresisGradient, i.e. what
+ * sbm_quantized_orientations(level = 1) returns as `angle` -- for a frame that already lies in device memory, written to
+ * the caller's device buffer d_angle (u8 one-hot labels, [h/2][w/2]), asynchronously on `stream` (NULL = the legacy default
+ * stream) of the CURRENT device.  The call allocates nothing (no cudaMalloc / cudaFree / cudaMallocHost, no context, no
+ * library that allocates): the pyrDown'ed image, the kernel's scratch, lives in a static device array of
+ * SBM_STATIC_SCRATCH_BYTES inside the library, which every GPU that loads the library holds until the process exits.
+ * A source whose level-1 image ((w/2) * (h/2) * channels bytes) exceeds that fails with SBM_ERR_CAPACITY and a message
+ * naming both sizes: the limit is a 2048 x 2048 x 3 source.  All calls on a device share the one array (it keeps the last
+ * call's image; each call overwrites every byte it later reads, so nothing has to be cleared): calls that overlap on the
+ * GPU -- different streams, or two host threads -- race; serialise them on one stream or with events.  The first call on a
+ * device looks the array's address up (cudaGetSymbolAddress); make that call outside stream capture.
+ * weak_threshold: the detector's weak threshold (magnitude > weak^2 qualifies a pixel, line2Dup.cpp:270). */
+#define SBM_STATIC_SCRATCH_BYTES (3 * 1024 * 1024)
+int sbm_quantized_level1_static(const uint8_t *d_img, int w, int h, int channels, float weak_threshold, uint8_t *d_angle, void *stream);
 
 /* Counters of the most recent frame: [0] coarse evaluations (sum over matched templates of
  * in-image features * template_positions), [1] coarse candidates, [2] local evaluations,

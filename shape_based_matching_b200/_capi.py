@@ -19,7 +19,7 @@ SYMBOLS = [
     "sbm_finalize_records", "sbm_set_debug", "sbm_get_intermediate", "sbm_similarity_map", "sbm_similarity_local",
     "sbm_last_stats", "sbm_last_timing", "sbm_set_timing", "sbm_match_batch", "sbm_match_batch_device", "sbm_time_similarity", "sbm_time_kernels", "sbm_quantized_orientations", "sbm_merge_shard_records", "sbm_time_l2_read",
     "sbm_set_candidate_capacity", "sbm_group_unique_id", "sbm_group_create", "sbm_group_destroy", "sbm_group_info", "sbm_group_match",
-    "sbm_group_match_batch", "sbm_group_block_bytes", "sbm_group_match_batch_device", "sbm_group_finalize", "sbm_phase_degrees",
+    "sbm_group_match_batch", "sbm_group_block_bytes", "sbm_group_match_batch_device", "sbm_group_finalize", "sbm_phase_degrees", "sbm_quantized_level1_static",
 ]
 
 GROUP_TEMPLATES, GROUP_TEMPLATES_CONTIGUOUS, GROUP_FRAMES = 0, 1, 2
@@ -78,6 +78,7 @@ def lib():
         L.sbm_group_match_batch_device.argtypes = [vp, vp, C.c_size_t, ci, ci, ci, ci, cf, vp, ci, vp, ci, vp]
         L.sbm_group_finalize.argtypes = [vp, vp, ci, ci, vp, ci, ci, vp, ci, vp]
         L.sbm_phase_degrees.argtypes = [ci, vp, vp, ci, vp, vp]
+        L.sbm_quantized_level1_static.argtypes = [vp, ci, ci, ci, C.c_float, vp, vp]
         L.sbm_set_debug.argtypes = [vp, ci]
         L.sbm_set_timing.argtypes = [vp, ci]
         L.sbm_get_intermediate.argtypes = [vp, ci, ci, vp, C.c_size_t, C.POINTER(C.c_size_t)]

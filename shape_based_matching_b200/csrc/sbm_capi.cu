@@ -2826,6 +2826,73 @@ int sbm_quantized_orientations(sbm_ctx *c, const uint8_t *img, int w, int h, int
 }
 }
 
+// ------------------------------------------------------------------------------------------------
+// sbm_quantized_level1_static: pyramid level 1's quantised orientations for callers that cannot allocate (see the header).
+// The scratch -- the pyrDown'ed source that k_orient reads -- is this file-scope array: every GPU that loads the library
+// holds SBM_STATIC_SCRATCH_BYTES of it until the process exits.  In host code `g_static_scratch` is only a stand-in for
+// the symbol; its device address is asked for once per device (cudaGetSymbolAddress, that device current) and kept.
+// ------------------------------------------------------------------------------------------------
+static __device__ __align__(256) uint8_t g_static_scratch[SBM_STATIC_SCRATCH_BYTES];
+
+namespace
+{
+struct StaticScratch
+{
+    uint8_t *ptr = nullptr;
+    int sms = 0;
+};
+constexpr int STATIC_SCRATCH_MAX_DEVICES = 64;
+std::mutex g_static_mu;
+StaticScratch g_static_dev[STATIC_SCRATCH_MAX_DEVICES];
+} // namespace
+
+extern "C" int sbm_quantized_level1_static(const uint8_t *d_img, int w, int h, int channels, float weak_threshold, uint8_t *d_angle,
+                                           void *stream)
+{
+    if (!d_img || !d_angle)
+        return fail(SBM_ERR_BAD_ARG, "sbm_quantized_level1_static: d_img and d_angle must be device pointers");
+    if (channels != 1 && channels != 3)
+        return fail(SBM_ERR_BAD_ARG, "source must have 1 or 3 channels (got %d)", channels);
+    if (w < 2 || h < 2)
+        return fail(SBM_ERR_BAD_ARG, "image too small for pyramid level 1 (%d x %d)", w, h);
+    const int dw = w / 2, dh = h / 2;
+    const size_t need = (size_t)dw * dh * channels;
+    if (need > (size_t)SBM_STATIC_SCRATCH_BYTES)
+        return fail(SBM_ERR_CAPACITY, "sbm_quantized_level1_static: a %d x %d x %d source needs %zu bytes of scratch, the library's static array holds %d",
+                    w, h, channels, need, (int)SBM_STATIC_SCRATCH_BYTES);
+    int dev = -1;
+    CK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= STATIC_SCRATCH_MAX_DEVICES)
+        return fail(SBM_ERR_BAD_ARG, "device %d: at most %d devices", dev, STATIC_SCRATCH_MAX_DEVICES);
+    StaticScratch sc;
+    {
+        std::lock_guard<std::mutex> lock(g_static_mu);
+        if (!g_static_dev[dev].ptr) // set-up, once per device, with that device current
+        {
+            void *p = nullptr;
+            CK(cudaGetSymbolAddress(&p, g_static_scratch));
+            int sms = 0;
+            if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms < 1)
+                sms = 148;
+            g_static_dev[dev].sms = sms;
+            g_static_dev[dev].ptr = (uint8_t *)p;
+        }
+        sc = g_static_dev[dev];
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    // cv::pyrDown(src, src, Size(cols/2, rows/2)) into the static array (every byte k_orient reads below is written here,
+    // so nothing of the previous call's contents is seen and nothing needs clearing) ...
+    dim3 g((dw + 31) / 32, (dh + K1B_ROWS - 1) / K1B_ROWS);
+    if (channels == 3)
+        k_pyrdown<3><<<g, K1B_THREADS, 0, st>>>(d_img, w, h, sc.ptr, dw, dh);
+    else
+        k_pyrdown<1><<<g, K1B_THREADS, 0, st>>>(d_img, w, h, sc.ptr, dw, dh);
+    CK(cudaGetLastError());
+    // ... and quantizedOrientations + hysteresisGradient on it, straight into the caller's buffer
+    CK(launchOrient(sc.sms, channels, sc.ptr, dw, dh, nullptr, 0, dw, weak_threshold * weak_threshold, d_angle, st));
+    return 0;
+}
+
 #ifdef SBM_TRACE
 // experiments only (tools/stage_trace.py): the per-stage clock sums of K5a / K5b, optionally cleared
 extern "C" int sbm_trace_read(unsigned long long *out16, int reset)
