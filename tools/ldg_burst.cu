@@ -9,7 +9,7 @@
 #include <cstdint>
 #include <cstdio>
 
-template <int VEC, int N> __global__ void k(const uint32_t *__restrict__ buf, size_t warp_span_words, int row_stride_words, long long *cycles, uint32_t *sink)
+template <int VEC, int N, int NC = 1> __global__ void k(const uint32_t *__restrict__ buf, size_t warp_span_words, int row_stride_words, long long *cycles, uint32_t *sink)
 {
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     const uint32_t *p = buf + (size_t)warp * warp_span_words + lane * VEC;
@@ -20,7 +20,11 @@ template <int VEC, int N> __global__ void k(const uint32_t *__restrict__ buf, si
     for (int i = 0; i < N; ++i)
     {
         const uint32_t *q = p + (size_t)i * row_stride_words;
-        if (VEC == 1)
+        if (NC == 0 && VEC == 2) // plain LDG.E instead of LDG.E.CONSTANT
+            asm volatile("ld.global.v2.u32 {%0,%1}, [%2];" : "=r"(v[i][0]), "=r"(v[i][VEC > 1 ? 1 : 0]) : "l"(q));
+        else if (NC == 2 && VEC == 2) // L1 bypass
+            asm volatile("ld.global.cg.v2.u32 {%0,%1}, [%2];" : "=r"(v[i][0]), "=r"(v[i][VEC > 1 ? 1 : 0]) : "l"(q));
+        else if (VEC == 1)
             asm volatile("ld.global.nc.u32 %0, [%1];" : "=r"(v[i][0]) : "l"(q));
         else if (VEC == 2)
             asm volatile("ld.global.nc.v2.u32 {%0,%1}, [%2];" : "=r"(v[i][0]), "=r"(v[i][VEC > 1 ? 1 : 0]) : "l"(q));
@@ -44,7 +48,7 @@ template <int VEC, int N> __global__ void k(const uint32_t *__restrict__ buf, si
         cycles[0] = t1 - t0, cycles[1] = t2 - t0;
 }
 
-template <int VEC, int N> void run(const uint32_t *buf, size_t buf_words, int ctas, int warps, int row_stride_bytes, long long *d_c, uint32_t *sink)
+template <int VEC, int N, int NC = 1> void run(const uint32_t *buf, size_t buf_words, int ctas, int warps, int row_stride_bytes, long long *d_c, uint32_t *sink)
 {
     const size_t span = (size_t)N * row_stride_bytes / 4 + 64; // words per warp: all rows distinct
     if ((size_t)ctas * warps * span > buf_words)
@@ -54,9 +58,9 @@ template <int VEC, int N> void run(const uint32_t *buf, size_t buf_words, int ct
     }
     long long h[2];
     for (int rep = 0; rep < 3; ++rep)
-        k<VEC, N><<<ctas, warps * 32>>>(buf, span, row_stride_bytes / 4, d_c, sink);
+        k<VEC, N, NC><<<ctas, warps * 32>>>(buf, span, row_stride_bytes / 4, d_c, sink);
     cudaMemcpy(h, d_c, sizeof(h), cudaMemcpyDeviceToHost);
-    printf("  LDG.%-3d x %2d  rows %4d B apart, %3d CTAs x %d warps: issue %5lld cycles, all data there after %5lld cycles (%.0f per load, %.1f B/cycle/warp)\n", 32 * VEC, N,
+    printf("  %s LDG.%-3d x %2d  rows %4d B apart, %3d CTAs x %d warps: issue %5lld cycles, all data there after %5lld cycles (%.0f per load, %.1f B/cycle/warp)\n", NC == 1 ? ".nc" : NC == 0 ? "   " : ".cg", 32 * VEC, N,
            row_stride_bytes, ctas, warps, h[0], h[1], (double)h[1] / N, 128.0 * VEC * N / h[1]);
 }
 
@@ -83,6 +87,13 @@ int main()
         run<4, 8>(buf, words, 148, warps, 512, d_c, sink);
         run<4, 16>(buf, words, 148, warps, 512, d_c, sink);
     }
+    printf("plain and .cg loads instead of .nc, 4 warps per CTA\n");
+    run<2, 16, 0>(buf, words, 148, 4, 512, d_c, sink);
+    run<2, 32, 0>(buf, words, 148, 4, 512, d_c, sink);
+    run<2, 16, 2>(buf, words, 148, 4, 512, d_c, sink);
+    run<2, 32, 2>(buf, words, 148, 4, 512, d_c, sink);
+    run<2, 32, 0>(buf, words, 37, 4, 8, d_c, sink);
+    run<2, 32, 2>(buf, words, 37, 4, 8, d_c, sink);
     printf("the product's pattern: pairs of overlapping LDG.64 (second one 8 bytes further)\n");
     run<2, 32>(buf, words, 37, 4, 8, d_c, sink); // rows 8 B apart: 32 loads over the same three lines (all but the first hit or merge)
     const cudaError_t e = cudaDeviceSynchronize();
