@@ -66,14 +66,30 @@ int frameSlots()
 constexpr int COUNT_WORDS = 16; // [0..levels-1] stage counts, [10..11] u64 local evaluations
 constexpr uint32_t HEAD_RECS = 1024;
 
-// K1 tile height for a w x h level: 64x32 tiles unless that leaves the GPU under two CTAs per SM, then 64x16.
-// SBM_ORIENT_TH=8|16|28|32 forces one height (experiments).  sms: multiprocessors of the context's device.
+// K1 runs on the tensor cores (k_orient_mma: blur and Sobel as banded int8 matrix products) unless SBM_ORIENT_MMA=0
+// asks for the integer-pipe kernel k_orient; both produce the same bytes (the parity suite runs both).
+bool orientMma()
+{
+    static const bool on = !(getenv("SBM_ORIENT_MMA") && atoi(getenv("SBM_ORIENT_MMA")) == 0);
+    return on;
+}
+
+// K1 tile height for a w x h level.  k_orient: 64x32 tiles unless that leaves the GPU under two CTAs per SM, then 64x16.
+// k_orient_mma: 64 x (8 NT - 4): 28 rows, or 12 when 28 leave the GPU under two CTAs per SM.
+// SBM_ORIENT_TH=8|16|28|32 (k_orient) / 12|20|28|36 (k_orient_mma) forces one height (experiments).
+// sms: multiprocessors of the context's device.
 int orientTileH(int w, int h, int sms)
 {
     static const int forced = getenv("SBM_ORIENT_TH") ? atoi(getenv("SBM_ORIENT_TH")) : 0;
+    const int cols = (w + K1_TW - 1) / K1_TW;
+    if (orientMma())
+    {
+        if (forced == 12 || forced == 20 || forced == 28 || forced == 36)
+            return forced;
+        return cols * ((h + 27) / 28) >= 2 * sms ? 28 : 12;
+    }
     if (forced == 8 || forced == 16 || forced == 28 || forced == 32)
         return forced;
-    const int cols = (w + K1_TW - 1) / K1_TW;
     if (cols * ((h + 31) / 32) >= 2 * sms)
         return 32;
     // 64x28 tiles fill the 148 SMs evenly at 1024 rows (592 CTAs = 4 per SM; the kernel alone 13.6 -> 12.5 us) but the
@@ -83,6 +99,12 @@ int orientTileH(int w, int h, int sms)
 
 void *orientFunc(int ch, int th)
 {
+    if (orientMma())
+    {
+        if (ch == 3)
+            return th == 36 ? (void *)k_orient_mma<3, 5> : th == 28 ? (void *)k_orient_mma<3, 4> : th == 20 ? (void *)k_orient_mma<3, 3> : (void *)k_orient_mma<3, 2>;
+        return th == 36 ? (void *)k_orient_mma<1, 5> : th == 28 ? (void *)k_orient_mma<1, 4> : th == 20 ? (void *)k_orient_mma<1, 3> : (void *)k_orient_mma<1, 2>;
+    }
     if (ch == 3)
         return th == 32 ? (void *)k_orient<3, 32> : th == 28 ? (void *)k_orient<3, 28> : th == 16 ? (void *)k_orient<3, 16> : (void *)k_orient<3, 8>;
     return th == 32 ? (void *)k_orient<1, 32> : th == 28 ? (void *)k_orient<1, 28> : th == 16 ? (void *)k_orient<1, 16> : (void *)k_orient<1, 8>;
