@@ -110,6 +110,15 @@ void *orientFunc(int ch, int th)
     return th == 32 ? (void *)k_orient<1, 32> : th == 28 ? (void *)k_orient<1, 28> : th == 16 ? (void *)k_orient<1, 16> : (void *)k_orient<1, 8>;
 }
 
+// Measurement aid (tools/inflight_shares.py): SBM_DEBUG_SHRINK is a bit mask of graph kernels that are launched with ONE CTA
+// instead of their grid -- bit 0 orient L0, 1 spread L0, 2 pyrDown, 3 orient L1, 4 spread L1, 5 similarity, 6 refine.  The
+// results are then garbage; what the frame rate gains is what that kernel costs with several frames in flight.
+dim3 dbgGrid(int bit, dim3 g)
+{
+    static const int mask = getenv("SBM_DEBUG_SHRINK") ? atoi(getenv("SBM_DEBUG_SHRINK")) : 0;
+    return (mask >> bit) & 1 ? dim3(1, 1, 1) : g;
+}
+
 // one K1 launch on stream st (match path: no dump outputs)
 cudaError_t launchOrient(int sms, int ch, const uint8_t *src, int w, int h, const uint8_t *mask, int mask_shift, int mask_w, float weak_sq,
                          uint8_t *quant, cudaStream_t st)
@@ -1074,10 +1083,10 @@ int buildGraph(sbm_ctx *c, Slot &s, const uint8_t *src0, float threshold, bool w
             cudaGraphNode_t n_pyr;
             dim3 gp((G.w + 31) / 32, (G.h + K1B_ROWS - 1) / K1B_ROWS);
             void *f = c->c == 3 ? (void *)k_pyrdown<3> : (void *)k_pyrdown<1>;
-            if ((rc = addKernel(g, &n_pyr, dep_src, f, gp, dim3(K1B_THREADS), src, P.w, P.h, LB.d_src, G.w, G.h)))
+            if ((rc = addKernel(g, &n_pyr, dep_src, f, dbgGrid(2, gp), dim3(K1B_THREADS), src, P.w, P.h, LB.d_src, G.w, G.h)))
                 return rc;
             if (l == 1)
-                s.n_pyr1 = n_pyr, s.f_pyr1 = f, s.g_pyr1 = gp;
+                s.n_pyr1 = n_pyr, s.f_pyr1 = f, s.g_pyr1 = dbgGrid(2, gp);
             src = LB.d_src;
             prev_src_node = n_pyr;
             dep_src.assign(1, n_pyr);
@@ -1087,14 +1096,14 @@ int buildGraph(sbm_ctx *c, Slot &s, const uint8_t *src0, float threshold, bool w
         dim3 g1((G.w + K1_TW - 1) / K1_TW, (G.h + th - 1) / th);
         cudaGraphNode_t n_or, n_sp;
         int mask_shift = l, mask_w = c->w;
-        if ((rc = addKernel(g, &n_or, dep_src, orientFunc(c->c, th), g1, dim3(K1_THREADS), src, G.w, G.h, null_mask, mask_shift, mask_w, weak_sq,
+        if ((rc = addKernel(g, &n_or, dep_src, orientFunc(c->c, th), dbgGrid(l == 0 ? 0 : 3, g1), dim3(K1_THREADS), src, G.w, G.h, null_mask, mask_shift, mask_w, weak_sq,
                             LB.d_quant, null_f, null_f)))
             return rc;
         if (l == 0)
-            s.n_orient0 = n_or, s.f_orient0 = orientFunc(c->c, th), s.g_orient0 = g1;
+            s.n_orient0 = n_or, s.f_orient0 = orientFunc(c->c, th), s.g_orient0 = dbgGrid(0, g1);
         dim3 g2((G.w + K2_PW - 1) / K2_PW, (G.h + K2_PH - 1) / K2_PH);
         const uint8_t *qin = LB.d_quant;
-        if ((rc = addKernel(g, &n_sp, {n_or}, spreadFunc(G.T, G.nib, G.tiled, G.bits), g2, dim3(G.bits ? K2_THREADS_BITS : K2_THREADS), qin, G.w, G.h, LB.d_lm, null_dbg, null_dbg)))
+        if ((rc = addKernel(g, &n_sp, {n_or}, spreadFunc(G.T, G.nib, G.tiled, G.bits), dbgGrid(l == 0 ? 1 : 4, g2), dim3(G.bits ? K2_THREADS_BITS : K2_THREADS), qin, G.w, G.h, LB.d_lm, null_dbg, null_dbg)))
             return rc;
         spread_node[l] = n_sp;
         launches += 2;
@@ -1114,7 +1123,7 @@ int buildGraph(sbm_ctx *c, Slot &s, const uint8_t *src0, float threshold, bool w
         {
             const cudaGraphNode_t deps[2] = {n_memset, spread_node[L - 1]};
             cudaKernelNodeParams kp = {};
-            kp.func = CL.func, kp.gridDim = CL.grid, kp.blockDim = CL.block, kp.sharedMemBytes = 0, kp.kernelParams = CL.argv, kp.extra = nullptr;
+            kp.func = CL.func, kp.gridDim = dbgGrid(5, CL.grid), kp.blockDim = CL.block, kp.sharedMemBytes = 0, kp.kernelParams = CL.argv, kp.extra = nullptr;
             CK(cudaGraphAddKernelNode(&n_sim, g, deps, 2, &kp));
         }
         tail = n_sim;
@@ -1138,7 +1147,7 @@ int buildGraph(sbm_ctx *c, Slot &s, const uint8_t *src0, float threshold, bool w
             int raw_center = 0;
             unsigned long long *ev = reinterpret_cast<unsigned long long *>(s.d_counts + 10);
             cudaGraphNode_t n_ref;
-            if ((rc = addKernel(g, &n_ref, {tail, spread_node[l]}, refineFunc(G.tiled), dim3(refineGrid(c, G.tiled)), dim3(K6_THREADS), lm, tl, ff, cin, cin_cnt, in_cap,
+            if ((rc = addKernel(g, &n_ref, {tail, spread_node[l]}, refineFunc(G.tiled), dbgGrid(6, dim3(refineGrid(c, G.tiled))), dim3(K6_THREADS), lm, tl, ff, cin, cin_cnt, in_cap,
                                 out, out_cnt, out_cap, G.w, G.h, G.T, threshold, nodump, raw_center, ev)))
                 return rc;
             tail = n_ref;

@@ -2,6 +2,9 @@ import sys, time
 sys.path.insert(0, "tests"); sys.path.insert(0, ".")
 import numpy as np, torch
 from _fixtures import load_case, load_templates
+import shape_based_matching_b200._capi as capi
+if len(sys.argv) > 1:
+    capi.LIB_PATH = sys.argv[1]
 from shape_based_matching_b200 import Detector, DEVICE_REC
 sys.path.insert(0, ".")
 import bench
