@@ -75,8 +75,8 @@ bool orientMma()
 }
 
 // K1 tile height for a w x h level.  k_orient: 64x32 tiles unless that leaves the GPU under two CTAs per SM, then 64x16.
-// k_orient_mma: 64 x (8 NT - 4): 28 rows, or 12 when 28 leave the GPU under two CTAs per SM.
-// SBM_ORIENT_TH=8|16|28|32 (k_orient) / 12|20|28|36 (k_orient_mma) forces one height (experiments).
+// k_orient_mma: 64 x (8 NT - 4) = 36, 20 or 12 rows, see below.
+// SBM_ORIENT_TH=8|16|28|32 (k_orient) / 12|20|28|36|44 (k_orient_mma) forces one height (experiments).
 // sms: multiprocessors of the context's device.
 int orientTileH(int w, int h, int sms)
 {
@@ -84,9 +84,16 @@ int orientTileH(int w, int h, int sms)
     const int cols = (w + K1_TW - 1) / K1_TW;
     if (orientMma())
     {
-        if (forced == 12 || forced == 20 || forced == 28 || forced == 36)
+        if (forced == 12 || forced == 20 || forced == 28 || forced == 36 || forced == 44)
             return forced;
-        return cols * ((h + 27) / 28) >= 2 * sms ? 28 : 12;
+        // With several frames in flight a kernel costs its instruction count (tools/inflight_shares.py), and tall tiles
+        // have the smaller halo: M1 in flight 20.6 us per frame with 28 / 12 rows (levels 0 / 1), 20.1 with 28 / 28,
+        // 19.6 with 36 / 36, 20.2 with 44 / 44 (three CTAs per SM); alone, level 0 takes 9.6 us with 28 rows (592 CTAs =
+        // 4 per SM) and 11.3 with 36.  Small levels keep shorter tiles so that half the SMs have a CTA.
+        for (int th : {36, 20})
+            if (2 * cols * ((h + th - 1) / th) >= sms)
+                return th;
+        return 12;
     }
     if (forced == 8 || forced == 16 || forced == 28 || forced == 32)
         return forced;
@@ -102,8 +109,8 @@ void *orientFunc(int ch, int th)
     if (orientMma())
     {
         if (ch == 3)
-            return th == 36 ? (void *)k_orient_mma<3, 5> : th == 28 ? (void *)k_orient_mma<3, 4> : th == 20 ? (void *)k_orient_mma<3, 3> : (void *)k_orient_mma<3, 2>;
-        return th == 36 ? (void *)k_orient_mma<1, 5> : th == 28 ? (void *)k_orient_mma<1, 4> : th == 20 ? (void *)k_orient_mma<1, 3> : (void *)k_orient_mma<1, 2>;
+            return th == 44 ? (void *)k_orient_mma<3, 6> : th == 36 ? (void *)k_orient_mma<3, 5> : th == 28 ? (void *)k_orient_mma<3, 4> : th == 20 ? (void *)k_orient_mma<3, 3> : (void *)k_orient_mma<3, 2>;
+        return th == 44 ? (void *)k_orient_mma<1, 6> : th == 36 ? (void *)k_orient_mma<1, 5> : th == 28 ? (void *)k_orient_mma<1, 4> : th == 20 ? (void *)k_orient_mma<1, 3> : (void *)k_orient_mma<1, 2>;
     }
     if (ch == 3)
         return th == 32 ? (void *)k_orient<3, 32> : th == 28 ? (void *)k_orient<3, 28> : th == 16 ? (void *)k_orient<3, 16> : (void *)k_orient<3, 8>;
