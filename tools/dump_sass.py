@@ -12,7 +12,10 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "shape_based_matching_b200", "libsbm_b200.so")
 # the instantiations a default run launches (M1 / C4 / C5: colour and gray frames, T = {4, 8}) and the fallbacks
 WANTED = [
-    r"k_orient<3, 32, false>", r"k_orient<3, 16, false>", r"k_orient<1, 32, false>", r"k_pyrdown<3>", r"k_pyrdown<1>",
+    r"k_orient_mma<3, 5>", r"k_orient_mma<3, 3>", r"k_orient_mma<3, 2>", r"k_orient_mma<1, 5>",  # K1, default (36 / 20 / 12 rows)
+    r"k_orient<3, 32, false>", r"k_orient<3, 16, false>", r"k_orient<1, 32, false>",  # K1 with SBM_ORIENT_MMA=0
+    r"k_orient<3, 16, true>",  # training front end (magnitude / angle dumps)
+    r"k_pyrdown<3>", r"k_pyrdown<1>",
     r"k_spread_linearize<4, false, true, false", r"k_spread_linearize<8, false, false, true", r"k_spread_linearize<8, true, false, false",
     r"k_similarity_bits<3, false>", r"k_similarity_bits<6, false>", r"k_similarity_bits<9, false>", r"k_similarity_bits<3, true>",
     r"k_similarity_nib", r"k_similarity\(", r"k_refine_tiled", r"k_refine\(", r"k_export", r"k_overflow_flag",
@@ -52,10 +55,10 @@ def main():
         rows.append((short, n, ops))
     with open(os.path.join(out_dir, "SUMMARY.md"), "w") as f:
         f.write("# SASS at %s: static instruction mix per kernel (cuobjdump -sass, sm_100a)\n\n" % commit)
-        f.write("| kernel | instructions | top opcodes | TMA / tcgen05 |\n|---|---|---|---|\n")
+        f.write("| kernel | instructions | top opcodes | tensor-core / TMA instructions |\n|---|---|---|---|\n")
         for short, n, ops in sorted(rows):
-            special = [k for k in ops if k.startswith(("UTMA", "UTC", "TCGEN"))]
-            f.write("| `%s` | %d | %s | %s |\n" % (short, n, ", ".join("%s %d" % kv for kv in ops.most_common(8)), ", ".join(special) or "none (byte gather / stencil work: no tensor-core or bulk-copy instruction by design)"))
+            special = ["%s %d" % (k, v) for k, v in ops.items() if k.startswith(("UTMA", "UTC", "TCGEN", "IMMA", "HMMA"))]
+            f.write("| `%s` | %d | %s | %s |\n" % (short, n, ", ".join("%s %d" % kv for kv in ops.most_common(8)), ", ".join(special) or "none (byte gather / bit-plane work)"))
     print("wrote", len(rows), "listings to", out_dir)
 
 
