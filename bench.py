@@ -34,6 +34,10 @@ import sys
 import threading
 import time
 
+# eight frame graphs of two branches each in flight: more hardware queues than the default 8 (before CUDA is initialised;
+# the library asks for the same when it is loaded first)
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))

@@ -52,13 +52,19 @@ int fail(int code, const char *fmt, ...)
 
 constexpr int SBM_SLOTS = 8; // frame slots a context can hold
 // frame slots the batch entry points keep in flight (SBM_FRAME_SLOTS=1..8 overrides; see profiles/ for the sweep)
+// Eight frame graphs of two branches each want more than the default 8 hardware queues (false dependencies between unrelated
+// kernels otherwise: M1 in flight 19.3 -> 18.8 us per frame).  Only takes effect if CUDA is not initialised yet in this
+// process and the caller has not set the variable; a host that initialises CUDA first sets it itself.
+const int g_max_connections_set = setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);
+
 int frameSlots()
 {
     static const int n = [] {
         const char *e = getenv("SBM_FRAME_SLOTS");
         if (!e)
             e = getenv("SBM_DEVICE_SLOTS"); // older name
-        const int v = e ? atoi(e) : 6; // sweep on M1: 2 -> 41.5, 4 -> 33.2, 6 -> 31.8, 8 -> 32.1 us per frame
+        const int v = e ? atoi(e) : 8; // sweep on M1 (round 1): 2 -> 41.5, 4 -> 33.2, 6 -> 31.8, 8 -> 32.1 us per frame; now 6 -> 19.1, 8 -> 18.8
+                                       // (with CUDA_DEVICE_MAX_CONNECTIONS = 32: a frame graph has two branches, 8 slots want 16 queues)
         return v < 1 ? 1 : (v > SBM_SLOTS ? SBM_SLOTS : v);
     }();
     return n;
@@ -1907,6 +1913,24 @@ int groupMatchHost(sbm_ctx *c, const uint8_t *const *imgs, const uint8_t *const 
 extern "C"
 {
 const char *sbm_last_error(void) { return g_err.c_str(); }
+
+#ifdef SBM_TRACE
+// -DSBM_TRACE builds only (tools/timeline.py): copies the CTA records out (dst: cap records of 32 bytes) and resets the count
+int sbm_debug_timeline(void *dst, unsigned int cap, unsigned int *n)
+{
+    unsigned int have = 0;
+    CK(cudaDeviceSynchronize());
+    CK(cudaMemcpyFromSymbol(&have, sbm::g_timeline_n, sizeof have));
+    const unsigned int take = std::min(std::min(have, cap), sbm::TIMELINE_CAP);
+    if (dst && take)
+        CK(cudaMemcpyFromSymbol(dst, sbm::g_timeline, (size_t)take * sizeof(sbm::TimelineRec)));
+    const unsigned int zero = 0;
+    CK(cudaMemcpyToSymbol(sbm::g_timeline_n, &zero, sizeof zero));
+    if (n)
+        *n = take;
+    return 0;
+}
+#endif
 
 const char *sbm_build_info(void)
 {
