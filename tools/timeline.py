@@ -66,4 +66,20 @@ hist = np.bincount(kern_active.sum(0), minlength=7)
 print("time share with k kinds of kernels active, k = 0..6:", np.round(100 * hist / hist.sum(), 1))
 for kid in range(6):
     print("  %-10s active %.1f %% of the time" % (NAMES[kid], 100 * kern_active[kid].mean()))
+# registers / thread slots held per SM over time (registers per CTA from -Xptxas -v, rounded up as the hardware allocates them)
+REGS = {0: 64 * 256, 1: 72 * 128, 2: 32 * 256, 3: 128 * 128, 4: 72 * 256, 5: 32 * 256}
+THREADS = {0: 256, 1: 128, 2: 256, 3: 128, 4: 256, 5: 256}
+R = np.zeros((nsm, nb)); TH = np.zeros((nsm, nb))
+for a, b_, sm, kid in zip(t0, t1, r["smid"], r["kid"]):
+    i0, i1 = int(a / step_us), int(b_ / step_us) + 1
+    R[sm, i0:i1] += REGS[int(kid)]; TH[sm, i0:i1] += THREADS[int(kid)]
+core = slice(int(100 / step_us), int((span - 100) / step_us))  # steady state: 100 us trimmed at both ends
+print("steady state: registers held per SM mean %.0f of 65536 (%.0f %%), thread slots %.0f of 2048 (%.0f %%), CTAs %.2f" % (
+    R[:, core].mean(), 100 * R[:, core].mean() / 65536, TH[:, core].mean(), 100 * TH[:, core].mean() / 2048, (cta_res[core] / nsm).mean()))
+print("share of (SM, time) cells without room for another 16 K-register CTA: %.1f %%" % (100 * (R[:, core] > 65536 - 16384).mean()))
+print("register x time per frame (M register-us):")
+for k in np.unique(key):
+    m = key == k
+    print("  %-22s %6.1f" % ("%s (%d)" % (NAMES[int(k // 100000)], int(k % 100000)), REGS[int(k // 100000)] * (t1[m] - t0[m]).sum() / B / 1e6))
+print("  capacity: %.1f" % (65536 * nsm * span / B / 1e6))
 np.save("gpurun_out/timeline_records.npy", r)
