@@ -5,7 +5,7 @@ import os
 import numpy as np
 
 PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(PKG, "libsbm_b200.so")
+LIB_PATH = os.environ.get("SBM_LIB_PATH") or os.path.join(PKG, "libsbm_b200.so")  # SBM_LIB_PATH: variant builds (tools/build_variant.py)
 
 TEMPLATE_DESC = np.dtype([("width", "<i4"), ("height", "<i4"), ("tl_x", "<i4"), ("tl_y", "<i4"), ("num_features", "<i4")])
 FEATURE = np.dtype([("x", "<i4"), ("y", "<i4"), ("label", "<i4")])
