@@ -132,13 +132,48 @@ dim3 dbgGrid(int bit, dim3 g)
     return (mask >> bit) & 1 ? dim3(1, 1, 1) : g;
 }
 
+// k_orient_mma's stage A through the copy engine: the source image as a 2-D tensor of bytes [h][w * ch] whose box is the
+// tile's staged window (K1M<C, NT>: SROW bytes x NR rows).  cuTensorMapEncodeTiled is looked up through the runtime (no link
+// against libcuda).  Returns 1 when the kernel may use the map: 16-byte aligned rows (else its vector / byte loads serve),
+// SBM_ORIENT_TMA not 0.
+typedef CUresult (*TensorMapEncodeFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *, const cuuint32_t *,
+                                      const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+TensorMapEncodeFn tensorMapEncoder()
+{
+    static const TensorMapEncodeFn fn = [] {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess)
+            p = nullptr;
+        return (TensorMapEncodeFn)p;
+    }();
+    return fn;
+}
+int orientMap(CUtensorMap *map, const uint8_t *src, int w, int h, int ch, int th)
+{
+    static const bool on = orientMma() && !(getenv("SBM_ORIENT_TMA") && atoi(getenv("SBM_ORIENT_TMA")) == 0);
+    memset(map, 0, sizeof *map);
+    const size_t rowbytes = (size_t)w * ch;
+    if (!on || !tensorMapEncoder() || (rowbytes & 15) || (reinterpret_cast<uintptr_t>(src) & 15))
+        return 0;
+    const int nt = (th + 4) / 8, npc = (ch * (K1_TW + 4) + 15) / 16; // as K1M<C, NT>
+    const cuuint64_t gdim[2] = {(cuuint64_t)rowbytes, (cuuint64_t)h}, gstride[1] = {(cuuint64_t)rowbytes};
+    const cuuint32_t box[2] = {(cuuint32_t)(16 * (npc + 2)), (cuuint32_t)(8 * (nt + 1))}, estr[2] = {1, 1};
+    return tensorMapEncoder()(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<uint8_t *>(src), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                              CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS
+               ? 1
+               : 0;
+}
+
 // one K1 launch on stream st (match path: no dump outputs)
 cudaError_t launchOrient(int sms, int ch, const uint8_t *src, int w, int h, const uint8_t *mask, int mask_shift, int mask_w, float weak_sq,
                          uint8_t *quant, cudaStream_t st)
 {
     const int th = orientTileH(w, h, sms);
     float *nf = nullptr;
-    void *argv[] = {&src, &w, &h, &mask, &mask_shift, &mask_w, &weak_sq, &quant, &nf, &nf};
+    CUtensorMap map;
+    int use_tma = orientMap(&map, src, w, h, ch, th);
+    void *argv[] = {&src, &w, &h, &mask, &mask_shift, &mask_w, &weak_sq, &quant, &nf, &nf, &map, &use_tma};
     return cudaLaunchKernel(orientFunc(ch, th), dim3((w + K1_TW - 1) / K1_TW, (h + th - 1) / th), dim3(K1_THREADS), argv, 0, st);
 }
 
@@ -1109,8 +1144,10 @@ int buildGraph(sbm_ctx *c, Slot &s, const uint8_t *src0, float threshold, bool w
         dim3 g1((G.w + K1_TW - 1) / K1_TW, (G.h + th - 1) / th);
         cudaGraphNode_t n_or, n_sp;
         int mask_shift = l, mask_w = c->w;
+        CUtensorMap map;
+        const int use_tma = orientMap(&map, src, G.w, G.h, c->c, th);
         if ((rc = addKernel(g, &n_or, dep_src, orientFunc(c->c, th), dbgGrid(l == 0 ? 0 : 3, g1), dim3(K1_THREADS), src, G.w, G.h, null_mask, mask_shift, mask_w, weak_sq,
-                            LB.d_quant, null_f, null_f)))
+                            LB.d_quant, null_f, null_f, map, use_tma)))
             return rc;
         if (l == 0)
             s.n_orient0 = n_or, s.f_orient0 = orientFunc(c->c, th), s.g_orient0 = dbgGrid(0, g1);
@@ -1214,7 +1251,9 @@ int launchFrameGraph(sbm_ctx *c, Slot &s, const uint8_t *d_img, float threshold,
             int w = G.w, h = G.h, shift = 0, mask_w = c->w;
             uint8_t *q = s.lv[0].d_quant;
             float *null_f = nullptr;
-            void *argv[] = {&src, &w, &h, &null_mask, &shift, &mask_w, (void *)&weak_sq, &q, &null_f, &null_f};
+            CUtensorMap map;
+            int use_tma = orientMap(&map, src, w, h, c->c, orientTileH(w, h, c->sms));
+            void *argv[] = {&src, &w, &h, &null_mask, &shift, &mask_w, (void *)&weak_sq, &q, &null_f, &null_f, &map, &use_tma};
             cudaKernelNodeParams p = {};
             p.func = s.f_orient0, p.gridDim = s.g_orient0, p.blockDim = dim3(K1_THREADS), p.kernelParams = argv;
             CK(cudaGraphExecKernelNodeSetParams(s.gexec, s.n_orient0, &p));
