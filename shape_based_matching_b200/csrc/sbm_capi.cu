@@ -82,7 +82,7 @@ bool orientMma()
 
 // K1 tile height for a w x h level.  k_orient: 64x32 tiles unless that leaves the GPU under two CTAs per SM, then 64x16.
 // k_orient_mma: 64 x (8 NT - 4) = 36, 20 or 12 rows, see below.
-// SBM_ORIENT_TH=8|16|28|32 (k_orient) / 12|20|28|36|44 (k_orient_mma) forces one height (experiments).
+// SBM_ORIENT_TH=8|16|28|32 (k_orient) / 12|20|28|36 (k_orient_mma) forces one height (experiments).
 // sms: multiprocessors of the context's device.
 int orientTileH(int w, int h, int sms)
 {
@@ -90,11 +90,11 @@ int orientTileH(int w, int h, int sms)
     const int cols = (w + K1_TW - 1) / K1_TW;
     if (orientMma())
     {
-        if (forced == 12 || forced == 20 || forced == 28 || forced == 36 || forced == 44)
+        if (forced == 12 || forced == 20 || forced == 28 || forced == 36)
             return forced;
         // With several frames in flight a kernel costs its instruction count (tools/inflight_shares.py), and tall tiles
         // have the smaller halo: M1 in flight 20.6 us per frame with 28 / 12 rows (levels 0 / 1), 20.1 with 28 / 28,
-        // 19.6 with 36 / 36, 20.2 with 44 / 44 (three CTAs per SM); alone, level 0 takes 9.6 us with 28 rows (592 CTAs =
+        // 19.6 with 36 / 36, 20.2 with 44 / 44 (three CTAs per SM; that height is gone since a CTA holds two windows); alone, level 0 takes 9.6 us with 28 rows (592 CTAs =
         // 4 per SM) and 11.3 with 36.  Small levels keep shorter tiles so that half the SMs have a CTA.
         for (int th : {36, 20})
             if (2 * cols * ((h + th - 1) / th) >= sms)
@@ -115,8 +115,8 @@ void *orientFunc(int ch, int th)
     if (orientMma())
     {
         if (ch == 3)
-            return th == 44 ? (void *)k_orient_mma<3, 6> : th == 36 ? (void *)k_orient_mma<3, 5> : th == 28 ? (void *)k_orient_mma<3, 4> : th == 20 ? (void *)k_orient_mma<3, 3> : (void *)k_orient_mma<3, 2>;
-        return th == 44 ? (void *)k_orient_mma<1, 6> : th == 36 ? (void *)k_orient_mma<1, 5> : th == 28 ? (void *)k_orient_mma<1, 4> : th == 20 ? (void *)k_orient_mma<1, 3> : (void *)k_orient_mma<1, 2>;
+            return th == 36 ? (void *)k_orient_mma<3, 5> : th == 28 ? (void *)k_orient_mma<3, 4> : th == 20 ? (void *)k_orient_mma<3, 3> : (void *)k_orient_mma<3, 2>;
+        return th == 36 ? (void *)k_orient_mma<1, 5> : th == 28 ? (void *)k_orient_mma<1, 4> : th == 20 ? (void *)k_orient_mma<1, 3> : (void *)k_orient_mma<1, 2>;
     }
     if (ch == 3)
         return th == 32 ? (void *)k_orient<3, 32> : th == 28 ? (void *)k_orient<3, 28> : th == 16 ? (void *)k_orient<3, 16> : (void *)k_orient<3, 8>;
@@ -149,7 +149,7 @@ TensorMapEncodeFn tensorMapEncoder()
     }();
     return fn;
 }
-int orientMap(CUtensorMap *map, const uint8_t *src, int w, int h, int ch, int th)
+int orientMap(CUtensorMap *map, const uint8_t *src, int w, int h, int ch, int th, int sms)
 {
     static const bool on = orientMma() && !(getenv("SBM_ORIENT_TMA") && atoi(getenv("SBM_ORIENT_TMA")) == 0);
     memset(map, 0, sizeof *map);
@@ -159,10 +159,23 @@ int orientMap(CUtensorMap *map, const uint8_t *src, int w, int h, int ch, int th
     const int nt = (th + 4) / 8, npc = (ch * (K1_TW + 4) + 15) / 16; // as K1M<C, NT>
     const cuuint64_t gdim[2] = {(cuuint64_t)rowbytes, (cuuint64_t)h}, gstride[1] = {(cuuint64_t)rowbytes};
     const cuuint32_t box[2] = {(cuuint32_t)(16 * (npc + 2)), (cuuint32_t)(8 * (nt + 1))}, estr[2] = {1, 1};
-    return tensorMapEncoder()(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<uint8_t *>(src), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                              CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS
-               ? 1
-               : 0;
+    if (tensorMapEncoder()(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<uint8_t *>(src), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                           CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+        return 0;
+    // 2: a CTA takes two tiles and asks for both windows at once, where that still leaves every SM a CTA (M1 level 0: 464
+    // tiles -> 240 CTAs; alone 11.0 -> 13.5 us, with frames in flight 18.35 -> 18.1 us per frame: the second window arrives
+    // while the first is worked on, and waiting for the window is 1.5 of a CTA's 6.7 us).  SBM_ORIENT_TILES=1 / 2 forces it.
+    static const int forced = getenv("SBM_ORIENT_TILES") ? atoi(getenv("SBM_ORIENT_TILES")) : 0;
+    const int rows = (h + th - 1) / th, cols = (w + K1_TW - 1) / K1_TW;
+    if (forced == 1 || rows < 2)
+        return 1;
+    return forced == 2 || cols * ((rows + 1) / 2) >= sms ? 2 : 1;
+}
+// grid of a K1 launch: one CTA per 64 x th tile, or per two tiles one above the other (use_tma == 2)
+dim3 orientGrid(int w, int h, int th, int use_tma)
+{
+    const int rows = (h + th - 1) / th;
+    return dim3((w + K1_TW - 1) / K1_TW, use_tma == 2 ? (rows + 1) / 2 : rows);
 }
 
 // one K1 launch on stream st (match path: no dump outputs)
@@ -172,9 +185,9 @@ cudaError_t launchOrient(int sms, int ch, const uint8_t *src, int w, int h, cons
     const int th = orientTileH(w, h, sms);
     float *nf = nullptr;
     CUtensorMap map;
-    int use_tma = orientMap(&map, src, w, h, ch, th);
+    int use_tma = orientMap(&map, src, w, h, ch, th, sms);
     void *argv[] = {&src, &w, &h, &mask, &mask_shift, &mask_w, &weak_sq, &quant, &nf, &nf, &map, &use_tma};
-    return cudaLaunchKernel(orientFunc(ch, th), dim3((w + K1_TW - 1) / K1_TW, (h + th - 1) / th), dim3(K1_THREADS), argv, 0, st);
+    return cudaLaunchKernel(orientFunc(ch, th), orientGrid(w, h, th, use_tma), dim3(K1_THREADS), argv, 0, st);
 }
 
 struct ClassSet
@@ -1141,11 +1154,11 @@ int buildGraph(sbm_ctx *c, Slot &s, const uint8_t *src0, float threshold, bool w
             ++launches;
         }
         const int th = orientTileH(G.w, G.h, c->sms);
-        dim3 g1((G.w + K1_TW - 1) / K1_TW, (G.h + th - 1) / th);
+        CUtensorMap map;
+        const int use_tma = orientMap(&map, src, G.w, G.h, c->c, th, c->sms);
+        dim3 g1 = orientGrid(G.w, G.h, th, use_tma);
         cudaGraphNode_t n_or, n_sp;
         int mask_shift = l, mask_w = c->w;
-        CUtensorMap map;
-        const int use_tma = orientMap(&map, src, G.w, G.h, c->c, th);
         if ((rc = addKernel(g, &n_or, dep_src, orientFunc(c->c, th), dbgGrid(l == 0 ? 0 : 3, g1), dim3(K1_THREADS), src, G.w, G.h, null_mask, mask_shift, mask_w, weak_sq,
                             LB.d_quant, null_f, null_f, map, use_tma)))
             return rc;
@@ -1252,10 +1265,12 @@ int launchFrameGraph(sbm_ctx *c, Slot &s, const uint8_t *d_img, float threshold,
             uint8_t *q = s.lv[0].d_quant;
             float *null_f = nullptr;
             CUtensorMap map;
-            int use_tma = orientMap(&map, src, w, h, c->c, orientTileH(w, h, c->sms));
+            const int th = orientTileH(w, h, c->sms);
+            int use_tma = orientMap(&map, src, w, h, c->c, th, c->sms);
             void *argv[] = {&src, &w, &h, &null_mask, &shift, &mask_w, (void *)&weak_sq, &q, &null_f, &null_f, &map, &use_tma};
             cudaKernelNodeParams p = {};
-            p.func = s.f_orient0, p.gridDim = s.g_orient0, p.blockDim = dim3(K1_THREADS), p.kernelParams = argv;
+            // (the grid follows the frame: a frame whose address rules the tensor copy out gets one CTA per tile)
+            p.func = s.f_orient0, p.gridDim = dbgGrid(0, orientGrid(w, h, th, use_tma)), p.blockDim = dim3(K1_THREADS), p.kernelParams = argv;
             CK(cudaGraphExecKernelNodeSetParams(s.gexec, s.n_orient0, &p));
         }
         if (s.n_pyr1)

@@ -148,7 +148,8 @@ def test_orientation_kernels_by_environment():
     """K1 exists twice: k_orient_mma (blur and Sobel as int8 matrix products on the tensor cores, the default) and k_orient
     (integer pipe, SBM_ORIENT_MMA=0).  Both must produce the reference's quantised images byte for byte, k_orient_mma with its
     source window staged by the copy engine (cp.async.bulk.tensor, the default for 16-byte aligned rows) and by plain loads
-    (SBM_ORIENT_TMA=0), and at every tile height it is instantiated for (SBM_ORIENT_TH: 12, 20, 28, 36, 44 rows) -- the same parity tests in fresh processes:
+    (SBM_ORIENT_TMA=0), with one tile per CTA and with two (both windows requested at once: the default only on large levels, SBM_ORIENT_TILES=1 / 2),
+    and at every tile height it is instantiated for (SBM_ORIENT_TH: 12, 20, 28, 36 rows) -- the same parity tests in fresh processes:
     fixtures colour and gray (intermediates byte-exact), the synthetic configurations (odd and ragged widths, three levels,
     masks) and the edge cases."""
     import os
@@ -157,7 +158,7 @@ def test_orientation_kernels_by_environment():
 
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     for extra in (dict(SBM_ORIENT_MMA="0"), dict(SBM_ORIENT_TMA="0"), dict(SBM_ORIENT_TH="12"), dict(SBM_ORIENT_TH="20"), dict(SBM_ORIENT_TH="28"),
-                  dict(SBM_ORIENT_TH="44")):
+                  dict(SBM_ORIENT_TILES="1"), dict(SBM_ORIENT_TILES="2")):
         env = dict(os.environ, **extra)
         r = subprocess.run([sys.executable, "-m", "pytest", "-q", "-x", "-m", "gpu", "tests/test_gpu_vs_port.py::test_cuda_equals_port",
                             "tests/test_gpu_edge_cases.py::test_masks", "tests/test_gpu_edge_cases.py::test_frames_smaller_than_a_kernel_tile",

@@ -47,6 +47,10 @@ for k in np.unique(key):
     dur = t1[m] - t0[m]
     g = int(k % 100000)
     print("%-22s %8d %9.1f %12.2f %14.2f %16.1f" % ("%s (%d)" % (NAMES[int(k // 100000)], g), m.sum(), m.sum() / g, dur.mean(), np.percentile(dur, 90), dur.sum() / B))
+m = (r["kid"] == 0) & (r["grid"] == r["grid"][r["kid"] == 0].max())
+if m.any() and r["cta"][m].max() > 0:  # `cta` holds ns from a CTA's start to SBM_TRACE_MID (k_orient_mma: source window staged)
+    mid = r["cta"][m].astype(np.float64) * 1e-3
+    print("orient level 0: a CTA waits %.2f us (p90 %.2f) for its staged window, of %.2f us alive" % (mid.mean(), np.percentile(mid, 90), (t1[m] - t0[m]).mean()))
 # occupancy over time
 nsm = int(r["smid"].max()) + 1
 step_us = 0.25
@@ -67,8 +71,8 @@ print("time share with k kinds of kernels active, k = 0..6:", np.round(100 * his
 for kid in range(6):
     print("  %-10s active %.1f %% of the time" % (NAMES[kid], 100 * kern_active[kid].mean()))
 # registers / thread slots held per SM over time (registers per CTA from -Xptxas -v, rounded up as the hardware allocates them)
-REGS = {0: 64 * 256, 1: 72 * 128, 2: 32 * 256, 3: 128 * 128, 4: 72 * 256, 5: 32 * 256}
-THREADS = {0: 256, 1: 128, 2: 256, 3: 128, 4: 256, 5: 256}
+REGS = {0: 64 * 256, 1: 72 * 128, 2: 32 * 256, 3: 128 * 128, 4: 72 * 128, 5: 32 * 256}
+THREADS = {0: 256, 1: 128, 2: 256, 3: 128, 4: 128, 5: 256}
 R = np.zeros((nsm, nb)); TH = np.zeros((nsm, nb))
 for a, b_, sm, kid in zip(t0, t1, r["smid"], r["kid"]):
     i0, i1 = int(a / step_us), int(b_ / step_us) + 1
