@@ -1991,7 +1991,7 @@ const char *sbm_build_info(void)
 #define SBM_STR2(x) #x
 #define SBM_STR(x) SBM_STR2(x)
     return "shape_based_matching_b200 csrc: nvcc " SBM_STR(__CUDACC_VER_MAJOR__) "." SBM_STR(__CUDACC_VER_MINOR__)
-           " -gencode arch=compute_100a,code=sm_100a; kernels k_orient k_pyrdown k_spread_linearize k_similarity_bits k_similarity_nib k_similarity k_refine_tiled k_refine";
+           " -gencode arch=compute_100a,code=sm_100a; kernels k_orient_mma k_orient k_pyrdown k_spread_linearize k_similarity_bits k_similarity_nib k_similarity k_refine_tiled k_refine";
 }
 
 int sbm_create(const int *T, int levels, float weak, float strong, int num_features, int device, sbm_ctx **out)
