@@ -662,7 +662,7 @@ def main():
     pinned = torch.from_numpy(frames).pin_memory()
     pin_np = pinned.numpy()
     n_final = 0
-    frame_list = [pin_np[i] for i in range(B)]
+    frame_list = pin_np  # one [B, H, W, C] block of pinned memory (Detector.match_batch takes a list of frames as well)
     # N > 1: the group call, which also exchanges the lists (every rank ends up with the final lists of all ranks' frames)
     e2e_call = det.group_match_batch if world > 1 else det.match_batch
     e2e_call(frame_list, THRESHOLD, [cid])

@@ -182,15 +182,26 @@ class Detector:
         return self._batch(self._L.sbm_match_batch, frames, threshold, class_ids, masks, cap, len(frames))
 
     def _batch(self, fn, frames, threshold, class_ids, masks, cap, lists):
-        imgs = [self._img(f) for f in frames]
-        n = len(imgs)
-        if n == 0:
-            return []
-        h, w, c = imgs[0].shape
-        for f in imgs:
-            if f.shape != (h, w, c):
-                raise ValueError("all frames of a batch must have the same shape")
-        ptrs = (C.c_void_p * n)(*[f.ctypes.data for f in imgs])
+        if isinstance(frames, np.ndarray) and frames.ndim in (3, 4) and frames.dtype == np.uint8 and frames.flags.c_contiguous:
+            # one [N, H, W(, C)] block: the frame addresses are an arithmetic sequence, no per-frame work on the host
+            n = frames.shape[0]
+            if n == 0:
+                return []
+            h, w = frames.shape[1:3]
+            c = frames.shape[3] if frames.ndim == 4 else 1
+            imgs = frames  # keeps the block alive over the call
+            addr = frames.ctypes.data + np.arange(n, dtype=np.uint64) * np.uint64(h * w * c)
+            ptrs = (C.c_void_p * n).from_buffer(addr)
+        else:
+            imgs = [self._img(f) for f in frames]
+            n = len(imgs)
+            if n == 0:
+                return []
+            h, w, c = imgs[0].shape
+            for f in imgs:
+                if f.shape != (h, w, c):
+                    raise ValueError("all frames of a batch must have the same shape")
+            ptrs = (C.c_void_p * n)(*[f.__array_interface__["data"][0] for f in imgs])  # (f.ctypes.data builds a ctypes object per frame)
         mptrs, keep = None, []
         if masks is not None:
             for m in masks:
@@ -206,7 +217,7 @@ class Detector:
         cap = cap or 256 * lists
         begin = (C.c_int * (lists + 1))()
         while True:
-            out = np.zeros(cap, MATCH_REC)
+            out = np.empty(cap, MATCH_REC)  # the library writes begin[lists] records; nothing behind them is read
             rc = fn(self._h, ptrs, mptrs, n, w, h, c, 0, C.c_float(threshold), arr, ncls, out.ctypes.data_as(C.c_void_p), cap, begin)
             if rc == -3 and begin[lists] > cap:
                 cap = begin[lists]
@@ -219,7 +230,8 @@ class Detector:
         """packed records + list boundaries -> one array per list (views of one trimmed copy: a ctypes int per access and a
         numpy copy per list would cost more than the C side spends ordering a short list)"""
         b = np.frombuffer(begin, dtype=np.int32, count=lists + 1).tolist()
-        out = out[: b[lists]].copy()
+        # (copied as bytes: numpy copies a structured array field by field, 25 ns per record against a memcpy)
+        out = out.view(np.uint8)[: b[lists] * out.itemsize].copy().view(out.dtype)
         return [out[b[i] : b[i + 1]] for i in range(lists)]
 
     # ---- device-resident path (bench `value`, multi-GPU) ----------------------------------------
